@@ -1,0 +1,121 @@
+"""Seeded synthetic scenes + cameras for the benchmark workloads.
+
+Camera conventions follow the reference glue: ``viewmatrix = w2c^T`` and
+``projmatrix = viewmatrix @ opengl_proj^T`` (reference src/utils/utils.py:93-104), i.e. the same
+matrices ``getProjectionMatrix2`` builds (reference src/utils/graphics_utils.py:72-93).
+Everything here is host-side input generation; no rasterizer math.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, NamedTuple
+
+import torch
+
+# name -> (W, H, fx, fy, cx, cy, default P)
+WORKLOADS = {
+    # reference configs/TUM_RGBD/rgbd_dataset_freiburg1_desk.yaml:8-13
+    "c1": (640, 480, 517.306408, 516.469215, 318.643040, 255.313989, 50_000),
+    "c2": (640, 480, 517.306408, 516.469215, 318.643040, 255.313989, 300_000),
+    # reference configs/Replica/replica.yaml:49-55
+    "c3": (1200, 680, 600.0, 600.0, 599.5, 339.5, 500_000),
+    # 2x the 876x584 intrinsics of reference configs/scannetpp/281bc17764.yaml:9-14
+    "c4": (1752, 1168, 625.584, 626.960, 876.0, 584.0, 1_500_000),
+    "c5": (640, 480, 517.306408, 516.469215, 318.643040, 255.313989, 300_000),
+    # test-only shapes (ragged: 70x52 is not a multiple of the 16x16 tile)
+    "tiny": (64, 48, 51.7306408, 51.6469215, 31.8643040, 25.5313989, 300),
+    "ragged": (70, 52, 56.0, 55.0, 33.3, 27.1, 400),
+}
+
+
+class Camera(NamedTuple):
+    W: int
+    H: int
+    fx: float
+    fy: float
+    cx: float
+    cy: float
+    tanfovx: float
+    tanfovy: float
+    viewmatrix: torch.Tensor      # (4,4) = w2c^T
+    projmatrix: torch.Tensor      # (4,4) = viewmatrix @ P^T
+    projmatrix_raw: torch.Tensor  # (4,4) = P^T
+    campos: torch.Tensor          # (3,)
+    w2c: torch.Tensor             # (4,4)
+
+
+def make_camera(W, H, fx, fy, cx, cy, w2c=None, near=0.01, far=100.0) -> Camera:
+    if w2c is None:
+        w2c = torch.eye(4, dtype=torch.float32)
+    w2c = w2c.to(torch.float32).cpu()
+    P = torch.tensor(
+        [[2 * fx / W, 0.0, -(W - 2 * cx) / W, 0.0],
+         [0.0, 2 * fy / H, -(H - 2 * cy) / H, 0.0],
+         [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+         [0.0, 0.0, 1.0, 0.0]], dtype=torch.float32)
+    view = w2c.t().contiguous()
+    proj_raw = P.t().contiguous()
+    full = (view @ proj_raw).contiguous()
+    campos = torch.linalg.inv(w2c)[:3, 3].contiguous()
+    return Camera(W, H, fx, fy, cx, cy, W / (2 * fx), H / (2 * fy), view, full, proj_raw, campos, w2c)
+
+
+def rot_xy(deg_x: float, deg_y: float) -> torch.Tensor:
+    """w2c of a camera at the origin rotated by the given angles about x then y."""
+    ax, ay = math.radians(deg_x), math.radians(deg_y)
+    Rx = torch.tensor([[1, 0, 0], [0, math.cos(ax), -math.sin(ax)], [0, math.sin(ax), math.cos(ax)]])
+    Ry = torch.tensor([[math.cos(ay), 0, math.sin(ay)], [0, 1, 0], [-math.sin(ay), 0, math.cos(ay)]])
+    T = torch.eye(4)
+    T[:3, :3] = (Ry @ Rx).to(torch.float32)
+    return T
+
+
+def keyframe_views(workload: str, n_views: int = 8):
+    """The c4 keyframe batch: identity camera rotated +-4 degrees about x / y."""
+    W, H, fx, fy, cx, cy, _ = WORKLOADS[workload]
+    angles = [(0, 0), (4, 0), (-4, 0), (0, 4), (0, -4), (4, 4), (-4, -4), (4, -4)]
+    return [make_camera(W, H, fx, fy, cx, cy, rot_xy(*angles[i % len(angles)])) for i in range(n_views)]
+
+
+def make_scene(workload: str = "c2", P: int | None = None, seed: int = 0, M: int = 1,
+               device="cpu", outside: float = 0.05, behind: float = 0.02,
+               scale_range=(0.7, 2.5)) -> Dict[str, torch.Tensor]:
+    """Synthetic Gaussians per SURVEY 8(d): pixels uniform in the image (+5 % outside up to
+    1.5x the frustum, 2 % behind the camera), depth U(1,4) m, per-axis scale (z/fx)*U(0.7,2.5),
+    random unit quaternions, opacity sigmoid(N(0,1.5^2)), SH-DC U(-1.7,1.7)."""
+    W, H, fx, fy, cx, cy, P0 = WORKLOADS[workload]
+    P = int(P0 if P is None else P)
+    g = torch.Generator().manual_seed(int(seed))
+    u = torch.rand(P, generator=g) * W
+    v = torch.rand(P, generator=g) * H
+    z = 1.0 + 3.0 * torch.rand(P, generator=g)
+    sel = torch.rand(P, generator=g)
+    f_out, f_beh = float(outside), float(behind)
+    outside = sel < f_out
+    behind = (sel >= f_out) & (sel < f_out + f_beh)
+    uo = (torch.rand(P, generator=g) * 1.5 - 0.25) * W
+    vo = (torch.rand(P, generator=g) * 1.5 - 0.25) * H
+    u = torch.where(outside, uo, u)
+    v = torch.where(outside, vo, v)
+    z = torch.where(behind, -z, z)
+    x = (u + 0.5 - cx) / fx * z
+    y = (v + 0.5 - cy) / fy * z
+    means3D = torch.stack([x, y, z], dim=1)
+    scales = (z.abs() / fx)[:, None] * (scale_range[0] + (scale_range[1] - scale_range[0]) * torch.rand(P, 3, generator=g))
+    q = torch.randn(P, 4, generator=g)
+    rotations = q / q.norm(dim=1, keepdim=True)
+    opacities = torch.sigmoid(1.5 * torch.randn(P, 1, generator=g))
+    shs = torch.zeros(P, M, 3)
+    shs[:, 0, :] = torch.rand(P, 3, generator=g) * 3.4 - 1.7
+    if M > 1:
+        shs[:, 1:, :] = 0.1 * torch.randn(P, M - 1, 3, generator=g)
+    gt_color = torch.rand(3, H, W, generator=g)
+    gt_depth = 1.0 + 3.0 * torch.rand(1, H, W, generator=g)
+    out = dict(means3D=means3D, scales=scales, rotations=rotations, opacities=opacities, shs=shs,
+               gt_color=gt_color, gt_depth=gt_depth)
+    return {k: t.to(torch.float32).contiguous().to(device) for k, t in out.items()}
+
+
+def workload_camera(workload: str, w2c=None) -> Camera:
+    W, H, fx, fy, cx, cy, _ = WORKLOADS[workload]
+    return make_camera(W, H, fx, fy, cx, cy, w2c)

@@ -1,0 +1,34 @@
+"""Shared helpers for the parity tests (oracle is the checker, never the thing under test on GPU)."""
+import numpy as np
+import torch
+
+import oracle
+from eags_raster import scene
+
+
+def oracle_forward(cam, sc, degree=0, bg=(0, 0, 0), variant=0, colors_precomp=None, scale_modifier=1.0,
+                   skip_blend=False):
+    return oracle.forward(cam.W, cam.H, cam.tanfovx, cam.tanfovy, cam.viewmatrix.numpy(),
+                          cam.projmatrix.numpy(), cam.campos.numpy(), sc["means3D"].cpu().numpy(),
+                          sc["scales"].cpu().numpy(), sc["rotations"].cpu().numpy(),
+                          sc["opacities"].cpu().numpy(),
+                          shs=None if colors_precomp is not None else sc["shs"].cpu().numpy(),
+                          colors_precomp=colors_precomp, degree=degree, bg=bg, variant=variant,
+                          scale_modifier=scale_modifier, skip_blend=skip_blend)
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| (tensor-level relative error)."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def assert_close_rel(a, b, rtol, atol_frac, what=""):
+    """elementwise |a-b| <= rtol*|b| + atol_frac*max|b|"""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    tol = rtol * np.abs(b) + atol_frac * max(np.abs(b).max(), 1e-30)
+    bad = np.abs(a - b) > tol
+    assert not bad.any(), (f"{what}: {bad.sum()} / {bad.size} elements out of tolerance; worst abs err "
+                           f"{np.abs(a - b).max():.3e} (max|ref| {np.abs(b).max():.3e})")
