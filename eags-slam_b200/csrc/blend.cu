@@ -1,0 +1,443 @@
+// blend.cu -- per-16x16-tile alpha blending, forward and backward (sm_100a).
+//
+//   K6 blend_fwd : front-to-back blend of colour + depth + alpha/opacity (+ n_touched in variant B);
+//                  upstream forward.cu::renderCUDA, SURVEY.md A.3.
+//   K7 blend_bwd : back-to-front replay producing dL/d{mean2D, conic, opacity, colour, depth} per
+//                  Gaussian; upstream backward.cu::renderCUDA, SURVEY.md A.4.
+//
+// Both kernels read the *sorted, packed splat stream* written by sort_pack (binning.cu): a tile's
+// Gaussians are 48-byte records laid out contiguously in blend order, so a batch is one linear
+// cp.async.bulk (TMA bulk copy, UBLKCP) into shared memory, completion-tracked by an mbarrier and
+// multi-buffered so the copy of batch b+2 overlaps the blending of batch b.  Upstream instead gathers
+// id -> xy / conic / colour / depth from four arrays behind a __syncthreads per batch.
+//
+// blend_bwd replaces upstream's 10 global atomics per (pixel, Gaussian) pair by
+//   (1) a 12-shuffle transposing butterfly that reduces the 10 gradient components over the 32
+//       pixels of a warp (skipped altogether when no lane of the warp is touched by the Gaussian),
+//   (2) per-warp partial slabs in shared memory summed in fixed order once per batch, and
+//   (3) three 16-byte vector atomics per (tile, Gaussian) into a 48-byte accumulator row.
+// The walk starts at the tile's max n_contrib instead of the end of the list.
+//
+// Tensor cores are not used: blending is a per-pixel ordered recurrence, not a contraction; the
+// bound is the FP32/issue pipe.
+#include "kernels.h"
+
+namespace {
+
+constexpr int BLK = 256;
+constexpr unsigned FULL = 0xffffffffu;
+
+// ---- mbarrier / TMA bulk-copy helpers (PTX) ------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+// ================================================================================================
+// K6  blend forward
+// ================================================================================================
+constexpr int FWD_BATCH = 128;   // records per stage (6 KB)
+constexpr int FWD_STAGES = 3;
+
+struct FwdArgs {
+    int W, H, gx;
+    const EagsCtrl* ctrl;
+    long long capacity;
+    const uint2* ranges;
+    const float4* records;
+    const float* bg;
+    float* out_color;
+    float* out_depth;
+    float* out_third;
+    int32_t* n_touched;
+    float* final_T;
+    uint32_t* n_contrib;
+    uint32_t* tile_max;
+};
+
+template <bool VARIANT_B, bool TMA>
+__global__ void __launch_bounds__(BLK)
+blend_fwd_kernel(FwdArgs a) {
+    __shared__ __align__(128) float4 s_rec[FWD_STAGES][FWD_BATCH * 3];
+    __shared__ __align__(8) uint64_t s_bar[FWD_STAGES];
+    __shared__ int s_touched[VARIANT_B ? FWD_BATCH : 1];
+    __shared__ unsigned s_max;
+
+    if (a.ctrl->num_rendered > (unsigned long long)a.capacity) return;
+    const int tid = threadIdx.x;
+    const int tile = blockIdx.x;
+    const int tx = tile % a.gx, ty = tile / a.gx;
+    const uint2 rg = a.ranges[tile];
+    const int n = (int)(rg.y - rg.x);
+    const int px = tx * EAGS_TILE + (tid & 15), py = ty * EAGS_TILE + (tid >> 4);
+    const bool inside = px < a.W && py < a.H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float4* src = a.records + (size_t)3 * rg.x;
+    const int nb = (n + FWD_BATCH - 1) / FWD_BATCH;
+
+    if (tid == 0) {
+        s_max = 0;
+        if (TMA) {
+            for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+            mbar_fence_init();
+        }
+    }
+    if (VARIANT_B && tid < FWD_BATCH) s_touched[tid] = 0;
+    __syncthreads();
+    if (TMA && tid == 0) {
+        for (int b = 0; b < FWD_STAGES && b < nb; b++) {
+            const int cnt = min(FWD_BATCH, n - b * FWD_BATCH);
+            mbar_expect_tx(&s_bar[b], (uint32_t)cnt * 48u);
+            tma_bulk_g2s(&s_rec[b][0], src + (size_t)3 * b * FWD_BATCH, (uint32_t)cnt * 48u, &s_bar[b]);
+        }
+    }
+
+    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
+    unsigned last = 0;
+    const bool count_touched = VARIANT_B && a.n_touched != nullptr;
+    bool done = !inside;
+
+    for (int b = 0; b < nb; b++) {
+        const int base = b * FWD_BATCH;
+        const int cnt = min(FWD_BATCH, n - base);
+        int stage;
+        if (TMA) {
+            stage = b % FWD_STAGES;
+            mbar_wait(&s_bar[stage], (uint32_t)((b / FWD_STAGES) & 1));
+        } else {
+            stage = 0;
+            for (int k = tid; k < cnt * 3; k += BLK) s_rec[0][k] = src[(size_t)3 * base + k];
+            __syncthreads();
+        }
+        if (!done) {
+            const float4* rec = s_rec[stage];
+            for (int j = 0; j < cnt; j++) {
+                const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+                const float dx = r0.x - pxf, dy = r0.y - pyf;
+                const float power = -0.5f * (r1.x * dx * dx + r1.z * dy * dy) - r1.y * dx * dy;
+                if (power > 0.f) continue;
+                const float alpha = fminf(0.99f, r1.w * __expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1.f - alpha);
+                if (test_T < 0.0001f) { done = true; break; }
+                const float4 r2 = rec[3 * j + 2];
+                const float w = alpha * T;
+                C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
+                D += r0.w * w;
+                A += w;
+                if (VARIANT_B) {
+                    if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                }
+                T = test_T;
+                last = (unsigned)(base + j + 1);
+            }
+        }
+        const int ndone = __syncthreads_count(done ? 1 : 0);
+        if (VARIANT_B && count_touched) {
+            if (tid < cnt) {
+                const int v = s_touched[tid];
+                if (v) {
+                    atomicAdd(&a.n_touched[__float_as_uint(s_rec[stage][3 * tid].z)], v);
+                    s_touched[tid] = 0;
+                }
+            }
+            __syncthreads();
+        }
+        if (ndone == BLK) {
+            if (TMA)   // drain copies still in flight before the CTA's shared memory is released
+                for (int bb = b + 1; bb < nb && bb < b + FWD_STAGES; bb++)
+                    mbar_wait(&s_bar[bb % FWD_STAGES], (uint32_t)((bb / FWD_STAGES) & 1));
+            break;
+        }
+        if (TMA && tid == 0 && b + FWD_STAGES < nb) {
+            const int nbase = (b + FWD_STAGES) * FWD_BATCH;
+            const int ncnt = min(FWD_BATCH, n - nbase);
+            mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
+            tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
+        }
+    }
+
+    if (inside) {
+        const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
+        a.final_T[pix] = T;
+        a.n_contrib[pix] = last;
+        a.out_color[pix] = C0 + T * __ldg(a.bg);
+        a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
+        a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
+        a.out_depth[pix] = D;
+        a.out_third[pix] = VARIANT_B ? 1.f - T : A;
+    }
+    const unsigned m = __reduce_max_sync(FULL, last);
+    if ((tid & 31) == 0 && m) atomicMax(&s_max, m);
+    __syncthreads();
+    if (tid == 0) a.tile_max[tile] = s_max;
+}
+
+// ================================================================================================
+// K7  blend backward
+// ================================================================================================
+constexpr int BWD_BATCH = 64;    // records per stage (3 KB); also the width of the per-warp bitmask
+constexpr int BWD_STAGES = 3;
+constexpr int PART_STRIDE = 11;  // 10 components + 1 pad: conflict-free column reads in the flush
+
+struct BwdArgs {
+    int W, H, gx;
+    const uint2* ranges;
+    const float4* records;
+    const uint32_t* tile_max;
+    const float* final_T;
+    const uint32_t* n_contrib;
+    const float* bg;
+    const float* dL_dcolor;
+    const float* dL_ddepth;
+    const float* dL_dthird;   // nullable
+    float4* grad_acc;         // [P][3]
+};
+
+// Sum v[0..9] over the 32 lanes with 12 shuffles.  Each stage halves the number of values a lane
+// owns while doubling the number of lanes already folded in.  On return lanes with `valid` hold
+// the warp total of component `slot` (two lanes per component; bit 0 of the lane distinguishes).
+__device__ __forceinline__ float butterfly10(const float v[10], int lane, int& slot, bool& valid) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+    float r[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const float send = b4 ? v[k] : v[k + 5];
+        const float keep = b4 ? v[k + 5] : v[k];
+        r[k] = keep + __shfl_xor_sync(FULL, send, 16);
+    }
+    float q[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float hi = (k + 3 < 5) ? r[k + 3] : 0.f;
+        const float send = b3 ? r[k] : hi;
+        const float keep = b3 ? hi : r[k];
+        q[k] = keep + __shfl_xor_sync(FULL, send, 8);
+    }
+    float p0, p1;
+    {
+        const float send0 = b2 ? q[0] : q[2];
+        const float keep0 = b2 ? q[2] : q[0];
+        p0 = keep0 + __shfl_xor_sync(FULL, send0, 4);
+        const float send1 = b2 ? q[1] : 0.f;
+        const float keep1 = b2 ? 0.f : q[1];
+        p1 = keep1 + __shfl_xor_sync(FULL, send1, 4);
+    }
+    const float send = b1 ? p0 : p1;
+    const float keep = b1 ? p1 : p0;
+    float o = keep + __shfl_xor_sync(FULL, send, 2);
+    o += __shfl_xor_sync(FULL, o, 1);
+    slot = (b4 ? 5 : 0) + (b3 ? 3 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
+    valid = !(b2 && b1) && !(b3 && b2);
+    return o;
+}
+
+template <bool TMA>
+__global__ void __launch_bounds__(BLK)
+blend_bwd_kernel(BwdArgs a) {
+    __shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 3];
+    __shared__ __align__(8) uint64_t s_bar[BWD_STAGES];
+    __shared__ float s_part[BLK / 32][BWD_BATCH][PART_STRIDE];
+    __shared__ unsigned long long s_mask[BLK / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const uint2 rg = a.ranges[tile];
+    const int n = min((int)(rg.y - rg.x), (int)a.tile_max[tile]);   // nothing past max n_contrib matters
+    if (n <= 0) return;
+    const int tx = tile % a.gx, ty = tile / a.gx;
+    const int px = tx * EAGS_TILE + (tid & 15), py = ty * EAGS_TILE + (tid >> 4);
+    const bool inside = px < a.W && py < a.H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float4* src = a.records + (size_t)3 * rg.x;
+    const int nb = (n + BWD_BATCH - 1) / BWD_BATCH;
+
+    if (TMA) {
+        if (tid == 0) {
+            for (int s = 0; s < BWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+            mbar_fence_init();
+        }
+        __syncthreads();
+        if (tid == 0) {
+            for (int bi = 0; bi < BWD_STAGES && bi < nb; bi++) {
+                const int base = (nb - 1 - bi) * BWD_BATCH;
+                const int cnt = min(BWD_BATCH, n - base);
+                mbar_expect_tx(&s_bar[bi], (uint32_t)cnt * 48u);
+                tma_bulk_g2s(&s_rec[bi][0], src + (size_t)3 * base, (uint32_t)cnt * 48u, &s_bar[bi]);
+            }
+        }
+    }
+
+    // per-pixel state
+    float T_final = 1.f, dC0 = 0.f, dC1 = 0.f, dC2 = 0.f, dD = 0.f, dA = 0.f;
+    int last_contributor = 0;
+    if (inside) {
+        const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
+        T_final = a.final_T[pix];
+        last_contributor = (int)a.n_contrib[pix];
+        dC0 = a.dL_dcolor[pix]; dC1 = a.dL_dcolor[HW + pix]; dC2 = a.dL_dcolor[2 * HW + pix];
+        dD = a.dL_ddepth[pix];
+        dA = a.dL_dthird ? a.dL_dthird[pix] : 0.f;
+    }
+    float T = T_final;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc_d = 0.f, acc_a = 0.f;
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
+    const float bg_dot = __ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2;
+    const float ddelx_dx = 0.5f * (float)a.W, ddely_dy = 0.5f * (float)a.H;
+
+    for (int bi = 0; bi < nb; bi++) {
+        const int base = (nb - 1 - bi) * BWD_BATCH;
+        const int cnt = min(BWD_BATCH, n - base);
+        int stage;
+        if (TMA) {
+            stage = bi % BWD_STAGES;
+            mbar_wait(&s_bar[stage], (uint32_t)((bi / BWD_STAGES) & 1));
+        } else {
+            stage = 0;
+            if (tid < cnt * 3) s_rec[0][tid] = src[(size_t)3 * base + tid];
+            __syncthreads();
+        }
+        const float4* rec = s_rec[stage];
+        unsigned long long wrote = 0ull;
+        for (int j = cnt - 1; j >= 0; j--) {
+            const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+            const float dx = r0.x - pxf, dy = r0.y - pyf;
+            const float power = -0.5f * (r1.x * dx * dx + r1.z * dy * dy) - r1.y * dx * dy;
+            const float G = __expf(power);
+            const float alpha = fminf(0.99f, r1.w * G);
+            const bool active = inside && (base + j < last_contributor) && (power <= 0.f) &&
+                                (alpha >= 1.0f / 255.0f);
+            if (!__any_sync(FULL, active)) continue;   // warp-uniform
+            float v[10];
+#pragma unroll
+            for (int k = 0; k < 10; k++) v[k] = 0.f;
+            if (active) {
+                const float4 r2 = rec[3 * j + 2];
+                const float inv1ma = __fdividef(1.f, 1.f - alpha);
+                T = T * inv1ma;
+                const float w = alpha * T;
+                float dL_dalpha;
+                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = r2.x;
+                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = r2.y;
+                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = r2.z;
+                dL_dalpha = (r2.x - acc0) * dC0 + (r2.y - acc1) * dC1 + (r2.z - acc2) * dC2;
+                v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2;
+                acc_d = last_alpha * last_depth + (1.f - last_alpha) * acc_d; last_depth = r0.w;
+                dL_dalpha += (r0.w - acc_d) * dD;
+                v[9] = w * dD;
+                acc_a = last_alpha + (1.f - last_alpha) * acc_a;
+                dL_dalpha += (1.f - acc_a) * dA;
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final * inv1ma) * bg_dot;
+                const float dL_dG = r1.w * dL_dalpha;   // Q1: the 0.99 clamp is straight-through
+                const float gdx = G * dx, gdy = G * dy;
+                const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
+                const float dG_ddely = -gdy * r1.z - gdx * r1.y;
+                v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                v[1] = dL_dG * dG_ddely * ddely_dy;
+                v[2] = -0.5f * gdx * dx * dL_dG;
+                v[3] = -0.5f * gdx * dy * dL_dG;   // Q8: half the true off-diagonal derivative
+                v[4] = -0.5f * gdy * dy * dL_dG;
+                v[5] = G * dL_dalpha;
+            }
+            int slot;
+            bool valid;
+            const float tot = butterfly10(v, lane, slot, valid);
+            if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
+            wrote |= 1ull << j;
+        }
+        if (lane == 0) s_mask[warp] = wrote;
+        __syncthreads();
+        if (tid < cnt) {
+            float g[12];
+#pragma unroll
+            for (int k = 0; k < 12; k++) g[k] = 0.f;
+            bool any = false;
+#pragma unroll
+            for (int w = 0; w < BLK / 32; w++) {
+                if ((s_mask[w] >> tid) & 1ull) {
+                    any = true;
+#pragma unroll
+                    for (int k = 0; k < 10; k++) g[k] += s_part[w][tid][k];
+                }
+            }
+            if (any) {
+                const unsigned idx = __float_as_uint(rec[3 * tid].z);
+                float4* dst = a.grad_acc + (size_t)3 * idx;
+                atomicAdd(dst + 0, make_float4(g[0], g[1], g[2], g[3]));
+                atomicAdd(dst + 1, make_float4(g[4], g[5], g[6], g[7]));
+                atomicAdd(reinterpret_cast<float2*>(dst + 2), make_float2(g[8], g[9]));
+            }
+        }
+        __syncthreads();
+        if (TMA && tid == 0 && bi + BWD_STAGES < nb) {
+            const int nbase = (nb - 1 - (bi + BWD_STAGES)) * BWD_BATCH;
+            const int ncnt = min(BWD_BATCH, n - nbase);
+            mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
+            tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
+        }
+    }
+}
+
+}  // namespace
+
+int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
+                     int use_tma, cudaStream_t s) {
+    FwdArgs a;
+    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx;
+    a.ctrl = img.ctrl; a.capacity = bin.capacity; a.ranges = img.ranges; a.records = bin.records;
+    a.bg = v.bg; a.out_color = out.color; a.out_depth = out.depth; a.out_third = out.third;
+    a.n_touched = out.n_touched; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
+    a.tile_max = img.tile_max;
+    if (v.variant == EAGS_VARIANT_B) {
+        if (use_tma) blend_fwd_kernel<true, true><<<img.G, BLK, 0, s>>>(a);
+        else blend_fwd_kernel<true, false><<<img.G, BLK, 0, s>>>(a);
+    } else {
+        if (use_tma) blend_fwd_kernel<false, true><<<img.G, BLK, 0, s>>>(a);
+        else blend_fwd_kernel<false, false><<<img.G, BLK, 0, s>>>(a);
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
+                     float* grad_acc, int use_tma, cudaStream_t s) {
+    BwdArgs a;
+    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx;
+    a.ranges = img.ranges; a.records = bin.records; a.tile_max = img.tile_max;
+    a.final_T = img.final_T; a.n_contrib = img.n_contrib; a.bg = v.bg;
+    a.dL_dcolor = gin.dL_dcolor; a.dL_ddepth = gin.dL_ddepth; a.dL_dthird = gin.dL_dthird;
+    a.grad_acc = (float4*)grad_acc;
+    if (use_tma) blend_bwd_kernel<true><<<img.G, BLK, 0, s>>>(a);
+    else blend_bwd_kernel<false><<<img.G, BLK, 0, s>>>(a);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}

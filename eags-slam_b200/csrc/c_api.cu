@@ -1,0 +1,187 @@
+// c_api.cu -- the extern "C" boundary declared in include/eags_raster.h.
+// Stateless apart from two process-wide tuning knobs and a launch counter; never allocates, never
+// synchronises; every launch goes to the stream handed in.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+#include "kernels.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int> g_opt_tma{1};
+std::atomic<unsigned long long> g_launches{0};
+
+int fail(int code, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s", what);
+    return code;
+}
+int fail_cuda(const char* where) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaErrorUnknown;
+    snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+    return (int)e;
+}
+#define CHECK_LAUNCH(expr, where)                 \
+    do {                                          \
+        int n__ = (expr);                         \
+        if (n__ < 0) return fail_cuda(where);     \
+        g_launches.fetch_add((unsigned)n__);      \
+    } while (0)
+#define CHECK_CUDA(expr, where)                              \
+    do {                                                     \
+        if ((expr) != cudaSuccess) return fail_cuda(where);  \
+    } while (0)
+
+bool view_ok(const EagsView* v) {
+    return v && v->image_height > 0 && v->image_width > 0 && v->bg && v->viewmatrix && v->projmatrix &&
+           v->campos && v->sh_degree >= 0 && v->sh_degree <= 3 &&
+           (v->variant == EAGS_VARIANT_A || v->variant == EAGS_VARIANT_B);
+}
+bool gauss_ok(const EagsView* v, const EagsGaussians* g) {
+    if (!g || g->P < 0) return false;
+    if (g->P == 0) return true;
+    if (!g->means3D || !g->opacities) return false;
+    if ((g->shs != nullptr) == (g->colors_precomp != nullptr)) return false;
+    const bool sr = g->scales && g->rotations;
+    if (sr == (g->cov3D_precomp != nullptr)) return false;
+    if (g->shs && g->M < (v->sh_degree + 1) * (v->sh_degree + 1)) return false;
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int eags_abi_version(void) { return EAGS_ABI_VERSION; }
+const char* eags_last_error(void) { return g_err; }
+uint64_t eags_launch_count(void) { return g_launches.load(); }
+
+size_t eags_geom_state_bytes(int32_t P) { return geom_layout(P < 0 ? 0 : P).total; }
+size_t eags_image_state_bytes(int32_t W, int32_t H) { return image_layout(W < 1 ? 1 : W, H < 1 ? 1 : H).total; }
+size_t eags_binning_state_bytes(int64_t capacity, int32_t with_keys) {
+    return binning_layout(capacity, with_keys).total;
+}
+size_t eags_backward_scratch_bytes(int32_t P) { return scratch_layout(P < 0 ? 0 : P).total; }
+
+int eags_set_option(const char* name, int32_t value) {
+    if (name && !strcmp(name, "tma")) { g_opt_tma.store(value ? 1 : 0); return 0; }
+    return fail(EAGS_ERR_INVALID, "eags_set_option: unknown option");
+}
+int eags_get_option(const char* name, int32_t* value) {
+    if (name && value && !strcmp(name, "tma")) { *value = g_opt_tma.load(); return 0; }
+    return fail(EAGS_ERR_INVALID, "eags_get_option: unknown option");
+}
+
+int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                      void* image_state, int32_t* radii, uint64_t* num_rendered_pinned, void* stream) {
+    if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad view settings");
+    if (!gauss_ok(view, g)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad Gaussian inputs");
+    if (!image_state || (g->P > 0 && (!geom_state || !radii)))
+        return fail(EAGS_ERR_INVALID, "eags_forward_geom: null state buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int W = view->image_width, H = view->image_height;
+    ImageLayout IL = image_layout(W, H);
+    ImagePtrs img = image_ptrs(image_state, W, H);
+    GeomPtrs geom = geom_ptrs(geom_state, g->P);
+    // ctrl + tile_count are contiguous: one memset node
+    CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4, s), "memset(ctrl)");
+    CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, s), "preprocess_fwd");
+    CHECK_LAUNCH(launch_tile_scan(img, s), "tile_scan");
+    if (num_rendered_pinned)
+        CHECK_CUDA(cudaMemcpyAsync(num_rendered_pinned, &img.ctrl->num_rendered, sizeof(uint64_t),
+                                   cudaMemcpyDeviceToHost, s),
+                   "memcpy(num_rendered)");
+    return 0;
+}
+
+int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                        void* geom_state, void* image_state, void* binning_state, int64_t capacity,
+                        int32_t with_keys, const EagsImages* out, void* stream) {
+    if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_forward_render: bad view settings");
+    if (!g || g->P < 0 || !image_state || !binning_state || capacity < 0 || !out || !out->color ||
+        !out->depth || !out->third || (g->P > 0 && (!geom_state || !radii)))
+        return fail(EAGS_ERR_INVALID, "eags_forward_render: null buffer");
+    if (capacity >= (1ll << 32)) return fail(EAGS_ERR_INVALID, "eags_forward_render: capacity must be < 2^32");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int W = view->image_width, H = view->image_height;
+    ImagePtrs img = image_ptrs(image_state, W, H);
+    GeomPtrs geom = geom_ptrs(geom_state, g->P);
+    BinningPtrs bin = binning_ptrs(binning_state, capacity, with_keys);
+    if (out->n_touched && g->P > 0)
+        CHECK_CUDA(cudaMemsetAsync(out->n_touched, 0, (size_t)g->P * 4, s), "memset(n_touched)");
+    CHECK_LAUNCH(launch_duplicate(*view, g->P, radii, geom, img, bin, s), "duplicate");
+    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, s), "sort_pack");
+    CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), s), "blend_fwd");
+    return 0;
+}
+
+int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                  const void* geom_state, const void* image_state, const void* binning_state,
+                  int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
+                  void* scratch, void* stream) {
+    if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_backward: bad view settings");
+    if (!gauss_ok(view, g)) return fail(EAGS_ERR_INVALID, "eags_backward: bad Gaussian inputs");
+    if (!gin || !gin->dL_dcolor || !gin->dL_ddepth || !gout)
+        return fail(EAGS_ERR_INVALID, "eags_backward: null gradient struct");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (g->P == 0) {
+        if (gout->dL_dtau) CHECK_CUDA(cudaMemsetAsync(gout->dL_dtau, 0, 6 * sizeof(float), s), "memset(dtau)");
+        return 0;
+    }
+    if (!radii || !geom_state || !image_state || !binning_state || !scratch || !gout->dL_dmeans3D)
+        return fail(EAGS_ERR_INVALID, "eags_backward: null buffer");
+    const int W = view->image_width, H = view->image_height;
+    ImagePtrs img = image_ptrs(const_cast<void*>(image_state), W, H);
+    GeomPtrs geom = geom_ptrs(const_cast<void*>(geom_state), g->P);
+    BinningPtrs bin = binning_ptrs(const_cast<void*>(binning_state), capacity, 0);
+    ScratchLayout SL = scratch_layout(g->P);
+    float* grad_acc = (float*)((char*)scratch + SL.grad_acc);
+    double* pose_acc = (double*)((char*)scratch + SL.pose);
+    CHECK_CUDA(cudaMemsetAsync(scratch, 0, SL.pose + 256, s), "memset(scratch)");
+    CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, g_opt_tma.load(), s), "blend_bwd");
+    CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, s), "preprocess_bwd");
+    return 0;
+}
+
+int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t capacity,
+                    int32_t with_keys, const void* geom_state, const void* image_state,
+                    const void* binning_state, const void** ptr, int64_t* count, int32_t* elem_bytes) {
+    if (!what || !ptr || !count || !elem_bytes) return fail(EAGS_ERR_INVALID, "eags_state_view: null argument");
+    GeomLayout GL = geom_layout(P);
+    ImageLayout IL = image_layout(W, H);
+    BinningLayout BL = binning_layout(capacity, with_keys);
+    const char* gb = (const char*)geom_state;
+    const char* ib = (const char*)image_state;
+    const char* bb = (const char*)binning_state;
+    struct Row { const char* name; const char* base; size_t off; int64_t n; int32_t eb; };
+    const Row rows[] = {
+        {"xy", gb, GL.xy, P, 8},
+        {"conic_opacity", gb, GL.conic_opacity, P, 16},
+        {"rgbd", gb, GL.rgbd, P, 16},
+        {"tiles_touched", gb, GL.tiles_touched, P, 4},
+        {"clamped", gb, GL.clamped, P, 1},
+        {"ctrl", ib, IL.ctrl, 1, 64},
+        {"tile_count", ib, IL.tile_count, IL.G, 4},
+        {"ranges", ib, IL.ranges, IL.G, 8},
+        {"tile_max_contrib", ib, IL.tile_max, IL.G, 4},
+        {"final_T", ib, IL.final_T, IL.N, 4},
+        {"n_contrib", ib, IL.n_contrib, IL.N, 4},
+        {"point_list", bb, BL.point_list, capacity, 4},
+        {"point_list_keys", bb, BL.keys, with_keys ? capacity : 0, 8},
+        {"records", bb, BL.records, capacity * 3, 16},
+    };
+    for (const Row& r : rows) {
+        if (!strcmp(what, r.name)) {
+            if (!r.base) return fail(EAGS_ERR_INVALID, "eags_state_view: that state buffer was not given");
+            *ptr = r.base + r.off;
+            *count = r.n;
+            *elem_bytes = r.eb;
+            return 0;
+        }
+    }
+    return fail(EAGS_ERR_INVALID, "eags_state_view: unknown array name");
+}
+
+}  // extern "C"

@@ -1,0 +1,87 @@
+// kernels.h -- launchers of the sm_100a kernels (internal; the public ABI is include/eags_raster.h)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/eags_raster.h"
+#include "layout.h"
+
+struct GeomPtrs {
+    float2* xy;
+    float4* conic_opacity;
+    float4* rgbd;
+    uint32_t* tiles_touched;
+    uint8_t* clamped;
+};
+struct ImagePtrs {
+    EagsCtrl* ctrl;
+    uint32_t* tile_count;
+    uint32_t* tile_cursor;
+    uint2* ranges;
+    uint32_t* big_list;
+    uint32_t* tile_max;
+    float* final_T;
+    uint32_t* n_contrib;
+    int gx, gy, G;
+};
+struct BinningPtrs {
+    unsigned long long* unsorted;
+    uint32_t* point_list;
+    float4* records;
+    unsigned long long* keys;   // nullable
+    long long capacity;
+};
+
+static inline GeomPtrs geom_ptrs(void* base, int64_t P) {
+    GeomLayout L = geom_layout(P);
+    char* b = (char*)base;
+    GeomPtrs g;
+    g.xy = (float2*)(b + L.xy);
+    g.conic_opacity = (float4*)(b + L.conic_opacity);
+    g.rgbd = (float4*)(b + L.rgbd);
+    g.tiles_touched = (uint32_t*)(b + L.tiles_touched);
+    g.clamped = (uint8_t*)(b + L.clamped);
+    return g;
+}
+static inline ImagePtrs image_ptrs(void* base, int W, int H) {
+    ImageLayout L = image_layout(W, H);
+    char* b = (char*)base;
+    ImagePtrs p;
+    p.ctrl = (EagsCtrl*)(b + L.ctrl);
+    p.tile_count = (uint32_t*)(b + L.tile_count);
+    p.tile_cursor = (uint32_t*)(b + L.tile_cursor);
+    p.ranges = (uint2*)(b + L.ranges);
+    p.big_list = (uint32_t*)(b + L.big_list);
+    p.tile_max = (uint32_t*)(b + L.tile_max);
+    p.final_T = (float*)(b + L.final_T);
+    p.n_contrib = (uint32_t*)(b + L.n_contrib);
+    p.gx = L.gx; p.gy = L.gy; p.G = L.G;
+    return p;
+}
+static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys) {
+    BinningLayout L = binning_layout(cap, with_keys);
+    char* b = (char*)base;
+    BinningPtrs p;
+    p.unsorted = (unsigned long long*)(b + L.unsorted);
+    p.point_list = (uint32_t*)(b + L.point_list);
+    p.records = (float4*)(b + L.records);
+    p.keys = with_keys ? (unsigned long long*)(b + L.keys) : nullptr;
+    p.capacity = cap;
+    return p;
+}
+
+// Every launcher returns the number of kernels it launched (>= 0) or -1 after a launch error
+// (cudaGetLastError is left set for the caller).
+int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
+                          int32_t* radii, cudaStream_t s);
+int launch_tile_scan(ImagePtrs img, cudaStream_t s);
+int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs geom, ImagePtrs img,
+                     BinningPtrs bin, cudaStream_t s);
+int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, cudaStream_t s);
+int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
+                     int use_tma, cudaStream_t s);
+int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
+                     float* grad_acc, int use_tma, cudaStream_t s);
+int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
+                          GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
+                          double* pose_acc, cudaStream_t s);

@@ -1,0 +1,112 @@
+// layout.h -- how the three opaque state buffers are carved (host + device).
+//
+// HBM layout (all arrays 256-byte aligned inside their buffer, SoA so that per-Gaussian kernels
+// stream with unit stride and 16-byte vectors):
+//
+//   geom state   (per Gaussian, written by preprocess_fwd)
+//     xy            float2[P]   pixel-space mean
+//     conic_opacity float4[P]   inverse 2-D covariance (xx, xy, yy) + opacity
+//     rgbd          float4[P]   SH->RGB colour and view-space depth
+//     tiles_touched u32[P]
+//     clamped       u8[P]       bit c: colour channel c was clamped at 0 (gates dL/dsh)
+//
+//   image state  (per tile / per pixel)
+//     ctrl          Ctrl        counters, zeroed at the start of every forward
+//     tile_count    u32[G]      keys per tile (zeroed with ctrl; atomics in preprocess_fwd)
+//     tile_cursor   u32[G]      scatter cursor (tile_scan -> duplicate)
+//     ranges        uint2[G]    [start, end) of each tile in the sorted list
+//     big_list      u32[G]      tiles whose list does not fit the small sort CTA
+//     tile_max      u32[G]      max n_contrib over the tile's pixels (bounds the backward walk)
+//     final_T       f32[N]
+//     n_contrib     u32[N]
+//
+//   binning state (per (tile, Gaussian) key; `cap` = capacity)
+//     unsorted      u64[cap]    (depth_bits << 32 | gaussian) bucketed by tile, unsorted
+//     point_list    u32[cap]    sorted Gaussian indices (upstream: binningState.point_list)
+//     records       float4[3*cap]  the sorted, packed splat stream the blend kernels read:
+//                                  {x, y, idx, depth} {conic.xx, conic.xy, conic.yy, opacity} {r, g, b, 0}
+//     keys          u64[cap]    sorted (tile << 32 | depth_bits) keys, only when with_keys
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#define EAGS_TILE 16
+#define EAGS_SORT_SMALL_CAP 2048   // keys a 256-thread sort CTA holds in shared memory
+#define EAGS_SORT_BIG_CAP 16384    // keys a 1024-thread sort CTA holds in shared memory
+
+struct EagsCtrl {
+    unsigned long long num_rendered;   // K = sum tiles_touched (atomics in preprocess_fwd)
+    unsigned long long num_scanned;    // K as seen by tile_scan (debug cross-check)
+    unsigned int n_big;                // entries in big_list
+    unsigned int pad[11];
+};
+static_assert(sizeof(EagsCtrl) == 64, "ctrl block is 64 bytes");
+
+static inline size_t eags_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct GeomLayout {
+    size_t xy, conic_opacity, rgbd, tiles_touched, clamped, total;
+};
+static inline GeomLayout geom_layout(int64_t P) {
+    GeomLayout L;
+    size_t o = 0;
+    L.xy = o;            o += eags_align256((size_t)P * 8);
+    L.conic_opacity = o; o += eags_align256((size_t)P * 16);
+    L.rgbd = o;          o += eags_align256((size_t)P * 16);
+    L.tiles_touched = o; o += eags_align256((size_t)P * 4);
+    L.clamped = o;       o += eags_align256((size_t)P);
+    L.total = o + 256;
+    return L;
+}
+
+struct ImageLayout {
+    size_t ctrl, tile_count, tile_cursor, ranges, big_list, tile_max, final_T, n_contrib, total;
+    int gx, gy, G;
+    int64_t N;
+};
+static inline ImageLayout image_layout(int W, int H) {
+    ImageLayout L;
+    L.gx = (W + EAGS_TILE - 1) / EAGS_TILE;
+    L.gy = (H + EAGS_TILE - 1) / EAGS_TILE;
+    L.G = L.gx * L.gy;
+    L.N = (int64_t)W * H;
+    size_t o = 0;
+    L.ctrl = o;        o += 64;
+    L.tile_count = o;  o += eags_align256((size_t)L.G * 4 + 64) - 64;   // ctrl + tile_count: one memset
+    L.tile_cursor = o; o += eags_align256((size_t)L.G * 4);
+    L.ranges = o;      o += eags_align256((size_t)L.G * 8);
+    L.big_list = o;    o += eags_align256((size_t)L.G * 4);
+    L.tile_max = o;    o += eags_align256((size_t)L.G * 4);
+    L.final_T = o;     o += eags_align256((size_t)L.N * 4);
+    L.n_contrib = o;   o += eags_align256((size_t)L.N * 4);
+    L.total = o + 256;
+    return L;
+}
+
+struct BinningLayout {
+    size_t unsorted, point_list, records, keys, total;
+};
+static inline BinningLayout binning_layout(int64_t cap, int with_keys) {
+    BinningLayout L;
+    if (cap < 1) cap = 1;
+    size_t o = 0;
+    L.unsorted = o;   o += eags_align256((size_t)cap * 8);
+    L.point_list = o; o += eags_align256((size_t)cap * 4);
+    L.records = o;    o += eags_align256((size_t)cap * 48);
+    L.keys = o;       o += with_keys ? eags_align256((size_t)cap * 8) : 0;
+    L.total = o + 256;
+    return L;
+}
+
+// backward scratch: grad_acc float[P][12] | pose accumulators double[16]
+struct ScratchLayout {
+    size_t grad_acc, pose, total;
+};
+static inline ScratchLayout scratch_layout(int64_t P) {
+    ScratchLayout L;
+    size_t o = 0;
+    L.grad_acc = o; o += eags_align256((size_t)P * 48);
+    L.pose = o;     o += 256;
+    L.total = o + 256;
+    return L;
+}

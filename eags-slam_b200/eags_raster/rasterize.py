@@ -1,0 +1,373 @@
+"""Host side of the rasterizer: state buffers, stream plumbing and the autograd bridge.
+
+Mirrors what upstream's ``diff_gaussian_rasterization/__init__.py::_RasterizeGaussians`` does around
+its two pybind calls, but over the C ABI of ``include/eags_raster.h``:
+PyTorch allocates every buffer (geom / binning / image state, outputs, gradients) and hands raw
+device pointers plus the current stream to the library.
+
+Host synchronisation.  Upstream blocks on a device->host copy of ``num_rendered`` in the middle of
+every forward to size the binning buffers.  Here the forward is issued *optimistically*: stage 1
+(``eags_forward_geom``) enqueues an async copy of K into pinned memory, stage 2
+(``eags_forward_render``) is enqueued immediately against a binning buffer whose capacity is a
+running high-water mark, and only then does the host wait -- for the stage-1 event, not for the
+render -- so the GPU never idles.  If K exceeded the capacity the render kernels exited without
+touching memory and stage 2 is re-issued with a larger buffer.  ``set_sync_mode("exact")``
+reproduces upstream's behaviour (wait, then allocate exactly K); ``"nosync"`` never waits (for CUDA
+graph capture; an overflow raises on the next call).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+import weakref
+from typing import NamedTuple, Optional
+
+import torch
+
+from . import _lib
+from ._lib import EagsGaussians, EagsImageGrads, EagsImages, EagsInputGrads, EagsView
+
+_SYNC_MODES = ("optimistic", "exact", "nosync")
+_sync_mode = "optimistic"
+_MIN_CAPACITY = 1 << 16
+_capacity = {}            # device index -> high-water capacity (keys)
+_tls = threading.local()  # pinned K slots / pending overflow checks per thread
+
+
+def set_sync_mode(mode: str) -> None:
+    global _sync_mode
+    if mode not in _SYNC_MODES:
+        raise ValueError(f"sync mode must be one of {_SYNC_MODES}")
+    _sync_mode = mode
+
+
+def get_sync_mode() -> str:
+    return _sync_mode
+
+
+def reserve_capacity(device, num_keys: int) -> None:
+    """Pre-size the binning buffer (e.g. before ``nosync`` / graph capture)."""
+    idx = torch.device(device).index
+    idx = torch.cuda.current_device() if idx is None else idx
+    _capacity[idx] = max(_capacity.get(idx, 0), int(num_keys))
+
+
+class RasterState(NamedTuple):
+    """Everything the backward pass (and the parity tests) need from a forward pass."""
+    P: int
+    M: int
+    W: int
+    H: int
+    variant: int
+    capacity: int
+    with_keys: bool
+    num_rendered: int          # -1 in nosync mode (not known on the host)
+    radii: torch.Tensor
+    geom: torch.Tensor
+    image: torch.Tensor
+    binning: torch.Tensor
+
+
+# ---- small helpers -------------------------------------------------------------------------------
+_cont_cache = {}
+
+
+def _f32c(t: torch.Tensor, device) -> torch.Tensor:
+    """fp32 + contiguous + on ``device``.  The reference passes ``w2c.transpose(0, 1)`` views
+    (utils.py:97) every call; the materialised copy is cached per (tensor, version)."""
+    if t.dtype == torch.float32 and t.is_contiguous() and t.device == device:
+        return t
+    key = id(t)
+    hit = _cont_cache.get(key)
+    if hit is not None:
+        ref, ver, out = hit
+        if ref() is t and ver == t._version:
+            return out
+    out = t.detach().to(device=device, dtype=torch.float32).contiguous()
+    if len(_cont_cache) > 256:
+        _cont_cache.clear()
+    try:
+        _cont_cache[key] = (weakref.ref(t), t._version, out)
+    except TypeError:
+        pass
+    return out
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _pinned_slot() -> torch.Tensor:
+    slot = getattr(_tls, "slot", None)
+    if slot is None:
+        slot = torch.zeros(1, dtype=torch.int64).pin_memory()
+        _tls.slot = slot
+    return slot
+
+
+def _round_capacity(k: int) -> int:
+    k = max(int(k), _MIN_CAPACITY)
+    return (k + 0xFFFF) & ~0xFFFF
+
+
+def _make_view(s, variant: int, device) -> tuple:
+    bg = _f32c(s.bg, device)
+    vm = _f32c(s.viewmatrix, device)
+    pm = _f32c(s.projmatrix, device)
+    cp = _f32c(s.campos, device)
+    raw = getattr(s, "projmatrix_raw", None)
+    raw = None if raw is None else _f32c(raw, device)
+    v = EagsView(int(s.image_height), int(s.image_width), float(s.tanfovx), float(s.tanfovy),
+                 float(s.scale_modifier), int(s.sh_degree), int(variant), int(bool(s.prefiltered)),
+                 int(bool(s.debug)), bg.data_ptr(), vm.data_ptr(), pm.data_ptr(), _ptr(raw),
+                 cp.data_ptr())
+    return v, (bg, vm, pm, cp, raw)   # keep the tensors alive while the struct is in use
+
+
+def _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D):
+    return EagsGaussians(P, M, _ptr(means3D), _ptr(opacities), _ptr(shs), _ptr(colors_precomp),
+                         _ptr(scales), _ptr(rotations), _ptr(cov3D))
+
+
+def _prep(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
+    if t is None or t.numel() == 0:
+        return None
+    if t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
+        t = t.to(device=device, dtype=torch.float32).contiguous()
+    return t
+
+
+def _check_pending(idx: int) -> None:
+    pend = getattr(_tls, "pending", None)
+    if not pend:
+        return
+    keep = []
+    for (dev, ev, slot, cap) in pend:
+        if ev.query():
+            k = int(slot[0])
+            if k > cap:
+                _capacity[dev] = _round_capacity(int(k * 1.5))
+                _tls.pending = []
+                raise RuntimeError(
+                    f"eags_raster (nosync mode): a previous forward produced {k} keys but the binning "
+                    f"buffer held {cap}; its outputs were not rendered. Capacity has been raised.")
+        else:
+            keep.append((dev, ev, slot, cap))
+    _tls.pending = keep
+
+
+# ---- forward / backward over the C ABI ------------------------------------------------------------
+def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_precomp=None,
+                      scales=None, rotations=None, cov3D_precomp=None, want_n_touched=False,
+                      with_keys=False):
+    """Returns (color (3,H,W), depth (1,H,W), third (1,H,W), radii (P,), n_touched | None, state)."""
+    lib = _lib.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("eags_raster: tensors must live on a CUDA device (there is no CPU path)")
+    device = means3D.device
+    H, W = int(settings.image_height), int(settings.image_width)
+    with torch.cuda.device(device):
+        means3D = _prep(means3D, device)
+        P = 0 if means3D is None else int(means3D.shape[0])
+        opacities = _prep(opacities, device)
+        shs = _prep(shs, device)
+        colors_precomp = _prep(colors_precomp, device)
+        scales = _prep(scales, device)
+        rotations = _prep(rotations, device)
+        cov3D_precomp = _prep(cov3D_precomp, device)
+        if P > 0:
+            if (shs is None) == (colors_precomp is None):
+                raise ValueError("Please provide exactly one of either SHs or precomputed colors!")
+            if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                    ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+                raise ValueError("Please provide exactly one of either scale/rotation pair or "
+                                 "precomputed 3D covariance!")
+        M = int(shs.shape[1]) if shs is not None else 0
+        stream = torch.cuda.current_stream(device).cuda_stream
+        view, keep = _make_view(settings, variant, device)
+        g = _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations,
+                            cov3D_precomp)
+        u8 = dict(dtype=torch.uint8, device=device)
+        geom = torch.empty(lib.eags_geom_state_bytes(P), **u8)
+        image = torch.empty(lib.eags_image_state_bytes(W, H), **u8)
+        radii = torch.empty(P, dtype=torch.int32, device=device)
+        color = torch.empty(3, H, W, dtype=torch.float32, device=device)
+        depth = torch.empty(1, H, W, dtype=torch.float32, device=device)
+        third = torch.empty(1, H, W, dtype=torch.float32, device=device)
+        n_touched = torch.empty(P, dtype=torch.int32, device=device) if want_n_touched else None
+        imgs = EagsImages(color.data_ptr(), depth.data_ptr(), third.data_ptr(), _ptr(n_touched))
+        idx = device.index
+        mode = _sync_mode
+        if mode == "nosync":
+            _check_pending(idx)
+            slot = torch.zeros(1, dtype=torch.int64).pin_memory()
+        else:
+            slot = _pinned_slot()
+        _lib.check(lib.eags_forward_geom(C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(),
+                                         radii.data_ptr(), slot.data_ptr(), stream), "eags_forward_geom")
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(device))
+
+        def render(cap):
+            b = torch.empty(lib.eags_binning_state_bytes(cap, int(with_keys)), **u8)
+            _lib.check(lib.eags_forward_render(C.byref(view), C.byref(g), radii.data_ptr(),
+                                               geom.data_ptr(), image.data_ptr(), b.data_ptr(), cap,
+                                               int(with_keys), C.byref(imgs), stream),
+                       "eags_forward_render")
+            return b
+
+        if mode == "exact":
+            ev.synchronize()
+            K = int(slot[0])
+            cap = max(K, 1)
+            binning = render(cap)
+        else:
+            cap = _capacity.get(idx, 0) or _round_capacity(max(4 * P, _MIN_CAPACITY))
+            binning = render(cap)
+            if mode == "optimistic":
+                ev.synchronize()          # waits for stage 1 only; the render keeps the GPU busy
+                K = int(slot[0])
+                if K > cap:               # render kernels exited untouched: re-issue with room
+                    cap = _round_capacity(int(K * 1.25))
+                    binning = render(cap)
+                _capacity[idx] = max(_capacity.get(idx, 0), _round_capacity(int(K * 1.25)))
+            else:
+                K = -1
+                pend = getattr(_tls, "pending", None) or []
+                pend.append((idx, ev, slot, cap))
+                _tls.pending = pend
+                _capacity[idx] = cap
+        del keep
+        state = RasterState(P, M, W, H, variant, cap, bool(with_keys), K, radii, geom, image, binning)
+    return color, depth, third, radii, n_touched, state
+
+
+def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, colors_precomp, scales,
+                       rotations, cov3D_precomp, dL_dcolor, dL_ddepth, dL_dthird=None,
+                       want_shs=True, want_tau=False):
+    """Returns dict(means3D, means2D, opacities, shs | colors_precomp, scales, rotations |
+    cov3D_precomp, tau)."""
+    lib = _lib.load()
+    device = state.radii.device
+    P, M, H, W = state.P, state.M, state.H, state.W
+    with torch.cuda.device(device):
+        f32 = dict(dtype=torch.float32, device=device)
+        means3D = _prep(means3D, device)
+        opacities = _prep(opacities, device)
+        shs = _prep(shs, device)
+        colors_precomp = _prep(colors_precomp, device)
+        scales = _prep(scales, device)
+        rotations = _prep(rotations, device)
+        cov3D_precomp = _prep(cov3D_precomp, device)
+        dL_dcolor = _prep(dL_dcolor, device)
+        dL_ddepth = _prep(dL_ddepth, device)
+        dL_dthird = _prep(dL_dthird, device)
+        if dL_dcolor is None:
+            dL_dcolor = torch.zeros(3, H, W, **f32)
+        if dL_ddepth is None:
+            dL_ddepth = torch.zeros(1, H, W, **f32)
+        out = dict(
+            means3D=torch.empty(P, 3, **f32),
+            means2D=torch.empty(P, 3, **f32),
+            opacities=torch.empty(P, 1, **f32),
+            shs=torch.empty(P, M, 3, **f32) if (shs is not None and want_shs) else None,
+            colors_precomp=torch.empty(P, 3, **f32) if colors_precomp is not None else None,
+            scales=torch.empty(P, 3, **f32) if scales is not None else None,
+            rotations=torch.empty(P, 4, **f32) if rotations is not None else None,
+            cov3D_precomp=torch.empty(P, 6, **f32) if cov3D_precomp is not None else None,
+            tau=torch.empty(6, **f32) if want_tau else None,
+        )
+        stream = torch.cuda.current_stream(device).cuda_stream
+        view, keep = _make_view(settings, state.variant, device)
+        g = _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations,
+                            cov3D_precomp)
+        gin = EagsImageGrads(dL_dcolor.data_ptr(), dL_ddepth.data_ptr(), _ptr(dL_dthird))
+        gout = EagsInputGrads(_ptr(out["means3D"]), _ptr(out["means2D"]), _ptr(out["opacities"]),
+                              _ptr(out["shs"]), _ptr(out["colors_precomp"]), _ptr(out["scales"]),
+                              _ptr(out["rotations"]), _ptr(out["cov3D_precomp"]), _ptr(out["tau"]))
+        scratch = torch.empty(lib.eags_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
+        _lib.check(lib.eags_backward(C.byref(view), C.byref(g), state.radii.data_ptr(),
+                                     state.geom.data_ptr(), state.image.data_ptr(),
+                                     state.binning.data_ptr(), state.capacity, C.byref(gin),
+                                     C.byref(gout), scratch.data_ptr(), stream), "eags_backward")
+        del keep
+    return out
+
+
+def state_array(state: RasterState, name: str) -> torch.Tensor:
+    """Copy one named array out of the opaque state buffers (parity tests / debugging)."""
+    lib = _lib.load()
+    ptr, cnt, eb = C.c_void_p(0), C.c_int64(0), C.c_int32(0)
+    _lib.check(lib.eags_state_view(name.encode(), state.P, state.W, state.H, state.capacity,
+                                   int(state.with_keys), state.geom.data_ptr(), state.image.data_ptr(),
+                                   state.binning.data_ptr(), C.byref(ptr), C.byref(cnt), C.byref(eb)),
+               "eags_state_view")
+    for buf in (state.geom, state.image, state.binning):
+        off = (ptr.value or 0) - buf.data_ptr()
+        if 0 <= off < buf.numel():
+            raw = buf[off: off + cnt.value * eb.value].clone()
+            break
+    else:
+        raise RuntimeError("state array outside the state buffers")
+    dt = {"xy": (torch.float32, (-1, 2)), "conic_opacity": (torch.float32, (-1, 4)),
+          "rgbd": (torch.float32, (-1, 4)), "tiles_touched": (torch.int32, (-1,)),
+          "clamped": (torch.uint8, (-1,)), "tile_count": (torch.int32, (-1,)),
+          "ranges": (torch.int32, (-1, 2)), "tile_max_contrib": (torch.int32, (-1,)),
+          "final_T": (torch.float32, (state.H, state.W)), "n_contrib": (torch.int32, (state.H, state.W)),
+          "point_list": (torch.int32, (-1,)), "point_list_keys": (torch.int64, (-1,)),
+          "records": (torch.float32, (-1, 12)), "ctrl": (torch.int64, (-1,))}[name]
+    return raw.view(dt[0]).reshape(dt[1])
+
+
+# ---- autograd bridge -------------------------------------------------------------------------------
+class _Rasterize(torch.autograd.Function):
+    """Autograd node shared by both API flavours (upstream: ``_RasterizeGaussians``)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                cov3D_precomp, theta, rho, settings, variant):
+        color, depth, third, radii, n_touched, state = rasterize_forward(
+            settings, variant, means3D, opacities, shs, colors_precomp, scales, rotations,
+            cov3D_precomp, want_n_touched=(variant == _lib.VARIANT_B))
+        ctx.settings = settings
+        ctx.state = state
+        ctx.has = [t is not None and t.numel() > 0 for t in
+                   (shs, colors_precomp, scales, rotations, cov3D_precomp)]
+        ctx.want_tau = theta is not None or rho is not None
+        ctx.save_for_backward(*[t if t is not None else torch.empty(0) for t in
+                                (means3D, opacities, shs, colors_precomp, scales, rotations,
+                                 cov3D_precomp)])
+        ctx.mark_non_differentiable(radii)
+        if n_touched is not None:
+            ctx.mark_non_differentiable(n_touched)
+            return color, depth, third, radii, n_touched
+        return color, depth, third, radii
+
+    @staticmethod
+    def backward(ctx, g_color, g_depth, g_third, *unused):
+        means3D, opacities, shs, colors_precomp, scales, rotations, cov3D = [
+            t if t.numel() > 0 else None for t in ctx.saved_tensors]
+        st = ctx.state
+        needs = ctx.needs_input_grad
+        if st.P == 0:
+            z = lambda t: None if t is None else torch.zeros_like(t)
+            tau = torch.zeros(3, device=st.radii.device) if ctx.want_tau else None
+            return (z(means3D), None, z(shs), z(colors_precomp), z(opacities), z(scales), z(rotations),
+                    z(cov3D), tau, tau, None, None)
+        # variant B upstream drops the gradient of the opacity image; variant A carries dL/dalpha
+        g_third = g_third if st.variant == _lib.VARIANT_A else None
+        out = rasterize_backward(ctx.settings, st, means3D, opacities, shs, colors_precomp, scales,
+                                 rotations, cov3D, g_color, g_depth, g_third,
+                                 want_shs=bool(needs[2]), want_tau=ctx.want_tau)
+        tau = out["tau"]
+        g_rho = tau[:3] if tau is not None else None
+        g_theta = tau[3:] if tau is not None else None
+        return (out["means3D"], out["means2D"], out["shs"], out["colors_precomp"],
+                out["opacities"].view(opacities.shape),
+                out["scales"], out["rotations"], out["cov3D_precomp"], g_theta, g_rho, None, None)
+
+
+def rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                        cov3D_precomp, settings, variant, theta=None, rho=None):
+    return _Rasterize.apply(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                            cov3D_precomp, theta, rho, settings, variant)

@@ -1,0 +1,166 @@
+/*
+ * eags_raster.h -- C ABI of the B200-native (sm_100a) differentiable Gaussian-splatting rasterizer
+ * that replaces the two un-vendored CUDA extensions on EAGS-SLAM's hot path:
+ *
+ *   gaussian_rasterizer._C          (variant A; reference requirements.txt:21,
+ *                                    call sites src/utils/utils.py:105-117,149,174-184)
+ *   diff_gaussian_rasterization._C  (variant B "w-pose"; reference requirements.txt:22,
+ *                                    call sites src/gsr/renderer.py:59-73,75,131-142)
+ *
+ * Upstream binds three pybind entry points (`rasterize_gaussians`, `rasterize_gaussians_backward`,
+ * `mark_visible`); the reference never calls the third.  This header is what a Python/ctypes,
+ * pybind or cgo binding of that operator links against instead.  Plain C: pointers, sizes and a
+ * stream handle -- no torch types.
+ *
+ * Ownership: every buffer (inputs, outputs, the three state buffers, scratch) is allocated by the
+ * caller (PyTorch's caching allocator in the shipped binding) on the CURRENT device and passed as
+ * raw device pointers.  The library keeps no global state, never allocates device memory, never
+ * synchronises the host with the device and launches only on the stream it is given, so it is
+ * re-entrant: the reference's loop-closure thread (src/entities/lc.py:625) can render on another
+ * device while the main thread tracks/maps.
+ *
+ * Errors: every entry point returns 0 on success or a negative EAGS_ERR_* / positive cudaError_t
+ * value; eags_last_error() gives a thread-local message.  There is no CPU fallback.
+ */
+#ifndef EAGS_RASTER_H
+#define EAGS_RASTER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EAGS_ABI_VERSION 1
+
+#define EAGS_VARIANT_A 0 /* third image = alpha = sum_i alpha_i T_i          (gaussian_rasterizer)          */
+#define EAGS_VARIANT_B 1 /* third image = opacity = 1 - T_final, + n_touched (diff_gaussian_rasterization)  */
+
+#define EAGS_ERR_INVALID -1   /* bad argument (null pointer, negative size, ...)  */
+#define EAGS_ERR_TOO_SMALL -2 /* a state buffer is smaller than eags_*_state_bytes */
+
+/* Per-view configuration == the reference's GaussianRasterizationSettings NamedTuple
+ * (src/utils/utils.py:105-117; variant B adds projmatrix_raw, src/gsr/renderer.py:59-73).
+ * Matrices are DEVICE pointers to 16 row-major floats exactly as the reference passes them:
+ * viewmatrix = w2c^T, projmatrix = viewmatrix @ P^T (utils.py:95-104, camera.py:97-107). */
+typedef struct EagsView {
+    int32_t image_height, image_width;
+    float tanfovx, tanfovy;
+    float scale_modifier;
+    int32_t sh_degree;  /* active SH degree 0..3 */
+    int32_t variant;    /* EAGS_VARIANT_A / EAGS_VARIANT_B */
+    int32_t prefiltered;
+    int32_t debug;
+    const float* bg;             /* device (3)  */
+    const float* viewmatrix;     /* device (16) */
+    const float* projmatrix;     /* device (16) */
+    const float* projmatrix_raw; /* device (16) or NULL; carried for ABI parity with variant B */
+    const float* campos;         /* device (3)  */
+} EagsView;
+
+/* The Gaussians handed to GaussianRasterizer.forward (utils.py:162-184, renderer.py:131-142).
+ * All device pointers, contiguous fp32.  Exactly one of shs / colors_precomp and exactly one of
+ * (scales, rotations) / cov3D_precomp is non-NULL. */
+typedef struct EagsGaussians {
+    int32_t P;                   /* number of Gaussians                              */
+    int32_t M;                   /* SH coefficients per Gaussian (stride of shs)     */
+    const float* means3D;        /* (P,3)                                            */
+    const float* opacities;      /* (P,1) post-sigmoid                               */
+    const float* shs;            /* (P,M,3) or NULL                                  */
+    const float* colors_precomp; /* (P,3)   or NULL                                  */
+    const float* scales;         /* (P,3) post-exp or NULL                           */
+    const float* rotations;      /* (P,4) wxyz, normalised, or NULL                  */
+    const float* cov3D_precomp;  /* (P,6) xx,xy,xz,yy,yz,zz or NULL                  */
+} EagsGaussians;
+
+/* Images produced by the forward pass; all device, caller-allocated. */
+typedef struct EagsImages {
+    float* color;       /* (3,H,W)                                                     */
+    float* depth;       /* (1,H,W)  sum_i z_i alpha_i T_i (not normalised)             */
+    float* third;       /* (1,H,W)  alpha (variant A) or opacity (variant B)           */
+    int32_t* n_touched; /* (P) or NULL; variant B: #pixels where the Gaussian was blended with T > 0.5 */
+} EagsImages;
+
+/* Gradients w.r.t. the images (inputs of the backward pass). */
+typedef struct EagsImageGrads {
+    const float* dL_dcolor; /* (3,H,W)          */
+    const float* dL_ddepth; /* (1,H,W)          */
+    const float* dL_dthird; /* (1,H,W) or NULL  */
+} EagsImageGrads;
+
+/* Gradients w.r.t. the operator inputs (outputs of the backward pass).  Any pointer may be NULL
+ * (that gradient is skipped) except dL_dmeans3D.  All are fully written (zeros for culled
+ * Gaussians). */
+typedef struct EagsInputGrads {
+    float* dL_dmeans3D;        /* (P,3) */
+    float* dL_dmeans2D;        /* (P,3) screen-space gradient (x,y,0): lands in means2D.grad   */
+    float* dL_dopacities;      /* (P,1) */
+    float* dL_dshs;            /* (P,M,3) */
+    float* dL_dcolors_precomp; /* (P,3) */
+    float* dL_dscales;         /* (P,3) */
+    float* dL_drotations;      /* (P,4) */
+    float* dL_dcov3D_precomp;  /* (P,6) */
+    float* dL_dtau;            /* (6) = [rho(3), theta(3)]: camera-pose gradient of the left
+                                  perturbation T_CW <- Exp(tau) T_CW (pose_utils.py:76-93)     */
+} EagsInputGrads;
+
+int eags_abi_version(void);
+const char* eags_last_error(void);
+
+/* Sizes of the three opaque state buffers (upstream: geomBuffer / binningBuffer / imgBuffer)
+ * and of the backward scratch.  `capacity` is the number of (tile, Gaussian) keys the binning
+ * buffer can hold; `with_keys` != 0 also reserves the sorted 64-bit (tile|depth) key list. */
+size_t eags_geom_state_bytes(int32_t P);
+size_t eags_image_state_bytes(int32_t width, int32_t height);
+size_t eags_binning_state_bytes(int64_t capacity, int32_t with_keys);
+size_t eags_backward_scratch_bytes(int32_t P);
+
+/* Forward, stage 1: per-Gaussian preprocess (cull, EWA projection, conic, radius, tile rectangle,
+ * SH->RGB), per-tile counts and the tile scan.  Writes `radii` (P) and, when
+ * `num_rendered_pinned` is non-NULL, enqueues an async copy of K = sum(tiles_touched) (uint64)
+ * into that pinned host slot -- the caller decides when (if ever) to wait for it. */
+int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                      void* image_state, int32_t* radii, uint64_t* num_rendered_pinned,
+                      void* stream);
+
+/* Forward, stage 2: key duplication, per-tile (depth, index) sort, packing of the sorted splat
+ * stream, and front-to-back blending.  If K > capacity nothing is rendered (all kernels exit);
+ * the caller re-issues this stage with a larger binning buffer. */
+int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                        void* geom_state, void* image_state, void* binning_state,
+                        int64_t capacity, int32_t with_keys, const EagsImages* out, void* stream);
+
+/* Backward: blend backward (warp-reduced, <= 1 vector atomic per (tile, Gaussian)) and preprocess
+ * backward (+ closed-form camera-pose gradient when dL_dtau is non-NULL). */
+int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                  const void* geom_state, const void* image_state, const void* binning_state,
+                  int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
+                  void* scratch, void* stream);
+
+/* Introspection of the state buffers (parity tests, debugging).  `what` selects the array; the
+ * function returns its device address, element count and element size.  Names:
+ *   "xy" float2[P], "conic_opacity" float4[P], "rgbd" float4[P] (r,g,b,depth),
+ *   "tiles_touched" u32[P], "clamped" u8[P] (bit c = channel c clamped),
+ *   "ranges" uint2[G], "tile_count" u32[G], "final_T" f32[N], "n_contrib" u32[N],
+ *   "tile_max_contrib" u32[G], "point_list" u32[cap], "point_list_keys" u64[cap] (with_keys),
+ *   "records" float4[3*cap]. */
+int eags_state_view(const char* what, int32_t P, int32_t width, int32_t height, int64_t capacity,
+                    int32_t with_keys, const void* geom_state, const void* image_state,
+                    const void* binning_state, const void** ptr, int64_t* count,
+                    int32_t* elem_bytes);
+
+/* Tuning knobs for A/B measurements (process-wide, read at launch time):
+ *   "tma"      1 (default): blend kernels stage splat batches with cp.async.bulk + mbarrier;
+ *              0: plain cooperative loads.                                                     */
+int eags_set_option(const char* name, int32_t value);
+int eags_get_option(const char* name, int32_t* value);
+
+/* Number of kernel launches issued by this library in the calling process since load (all
+ * threads); bench.py reports the per-step delta as `gpu_launches`. */
+uint64_t eags_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EAGS_RASTER_H */

@@ -32,3 +32,41 @@ def assert_close_rel(a, b, rtol, atol_frac, what=""):
     bad = np.abs(a - b) > tol
     assert not bad.any(), (f"{what}: {bad.sum()} / {bad.size} elements out of tolerance; worst abs err "
                            f"{np.abs(a - b).max():.3e} (max|ref| {np.abs(b).max():.3e})")
+
+
+# ---- GPU-side helpers (the CUDA path under test, called through the C ABI binding) ----------------
+class Settings:
+    """Duck-typed GaussianRasterizationSettings built from a scene.Camera (device tensors)."""
+
+    def __init__(self, cam, device, sh_degree=0, bg=(0, 0, 0), scale_modifier=1.0):
+        self.image_height, self.image_width = cam.H, cam.W
+        self.tanfovx, self.tanfovy = cam.tanfovx, cam.tanfovy
+        self.bg = torch.tensor(bg, dtype=torch.float32, device=device)
+        self.scale_modifier = scale_modifier
+        self.viewmatrix = cam.viewmatrix.to(device)
+        self.projmatrix = cam.projmatrix.to(device)
+        self.projmatrix_raw = cam.projmatrix_raw.to(device)
+        self.sh_degree = sh_degree
+        self.campos = cam.campos.to(device)
+        self.prefiltered = False
+        self.debug = False
+
+
+def cuda_forward(cam, sc, device="cuda", degree=0, bg=(0, 0, 0), variant=0, colors_precomp=None,
+                 cov3D_precomp=None, scale_modifier=1.0, with_keys=True):
+    from eags_raster import rasterize_forward
+    st = Settings(cam, device, degree, bg, scale_modifier)
+    d = {k: v.to(device) for k, v in sc.items()}
+    out = rasterize_forward(
+        st, variant, d["means3D"], d["opacities"],
+        shs=None if colors_precomp is not None else d["shs"],
+        colors_precomp=None if colors_precomp is None else torch.as_tensor(colors_precomp).to(device),
+        scales=None if cov3D_precomp is not None else d["scales"],
+        rotations=None if cov3D_precomp is not None else d["rotations"],
+        cov3D_precomp=None if cov3D_precomp is None else torch.as_tensor(cov3D_precomp).to(device),
+        want_n_touched=(variant == 1), with_keys=with_keys)
+    return st, d, out
+
+
+def nonfragile(o):
+    return o["fragile"] == 0
