@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- rasterizer fwd+bwd iterations/s on the BASELINE.json workloads.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2] [--impl ours|reference]
+
+One *step* = one pass of the hot path over one synthetic view: GaussianRasterizer forward ->
+L1 colour + L1 depth loss -> backward to means3D / opacities / scales / rotations.
+N = 1 runs BASELINE.json configs[1] (c2: 640x480, 300 K Gaussians, the tracking shape).  N > 1 is
+the sharded-mapping shape: every rank holds a replica of the same submap, renders its own keyframe
+view per step, and the per-Gaussian gradients (11 floats) are summed with one NCCL all-reduce
+(weak scaling: the per-GPU work is the N = 1 workload; value = view-iterations/s over all ranks).
+
+Timing: W >= 3 warm-up steps, then K steps each bracketed by CUDA events on the launching stream
+with an L2 flush (256 MiB write) before every step, outside the events; barrier +
+torch.cuda.synchronize() on both sides; max over ranks.  `e2e` repeats the measurement through
+the same public API with HOST (pinned) inputs: host->device copies of all Gaussian tensors and a
+device->host read of the loss inside every timed step.  `--impl reference` times the CPU oracle
+(the reference has no CPU implementation of this path and its CUDA kernels are un-vendored pip
+dependencies) on the box's host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "eags-slam_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "rasterizer fwd+bwd it/s"
+UNIT = "it/s"
+FP32_FLOPS_FWD_PAIR = 30.0
+FP32_FLOPS_BWD_PAIR = 90.0
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), src="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_workload(name, device, seed, view_id=0, P=None):
+    from eags_raster import scene
+    from gaussian_rasterizer import GaussianRasterizationSettings
+    sc = scene.make_scene(name, P=P, seed=seed)
+    if view_id == 0:
+        cam = scene.workload_camera(name)
+    else:
+        cam = scene.keyframe_views(name, 8)[view_id % 8]
+    s = GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+        bg=torch.zeros(3, device=device), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(device),
+        projmatrix=cam.projmatrix.to(device), sh_degree=0, campos=cam.campos.to(device),
+        prefiltered=False, debug=False)
+    return sc, cam, s
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from eags_raster import _lib, rasterize as rz, state_array
+    from gaussian_rasterizer import GaussianRasterizer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+    peaks = load_peaks()
+    wl = args.workload
+    # every rank: the SAME submap (seed 0), its own keyframe view
+    sc, cam, settings = make_workload(wl, dev, seed=0, view_id=rank if world > 1 else 0)
+    keys = ("means3D", "scales", "rotations", "opacities")
+    P = sc["means3D"].shape[0]
+    host = {k: sc[k].pin_memory() for k in keys + ("shs",)}
+    devt = {k: sc[k].to(dev) for k in keys + ("shs",)}
+    gt_c, gt_d = sc["gt_color"].to(dev), sc["gt_depth"].to(dev)
+    raster = GaussianRasterizer(raster_settings=settings)
+    # fused gradient buffer: 13 floats / Gaussian (xyz 3, scale 3, rot 4, opacity 1, +2 pad-free)
+    sizes = {"means3D": 3, "scales": 3, "rotations": 4, "opacities": 1}
+    flat_grad = torch.zeros(P * 11, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step(src, read_loss=False):
+        leaf = {k: src[k].detach().requires_grad_(True) for k in keys}
+        m2d = torch.zeros_like(leaf["means3D"], requires_grad=True)
+        color, depth, alpha, radii = raster(means3D=leaf["means3D"], means2D=m2d, opacities=leaf["opacities"],
+                                            shs=src["shs"], colors_precomp=None, scales=leaf["scales"],
+                                            rotations=leaf["rotations"], cov3D_precomp=None)
+        loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
+        loss.backward()
+        if world > 1:
+            off = 0
+            for k in keys:
+                n = P * sizes[k]
+                flat_grad[off:off + n].copy_(leaf[k].grad.reshape(-1))
+                off += n
+            dist.all_reduce(flat_grad)
+        return float(loss) if read_loss else loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up, then device-timed steps with inputs resident in HBM ----
+    for _ in range(max(args.warmup, 3)):
+        step(devt)
+    barrier()
+    l0 = _lib.launch_count()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    for a, b in evs:
+        flush.zero_()
+        a.record()
+        step(devt)
+        b.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = (_lib.launch_count() - l0) / args.steps
+    ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    # ---- e2e: host (pinned) inputs, H2D of every Gaussian tensor + D2H of the loss, per step ----
+    h2d_bytes = sum(host[k].numel() * 4 for k in host)
+    for _ in range(3):
+        step({k: host[k].to(dev, non_blocking=True) for k in host}, read_loss=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()
+        step({k: host[k].to(dev, non_blocking=True) for k in host}, read_loss=True)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    # ---- max over ranks ----
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = float(t[0]), float(t[1])
+
+    out = None
+    if rank == 0:
+        # per-kernel timing of one more forward/backward with events around each C-ABI stage
+        roof, kern = kernel_rooflines(settings, devt, gt_c, gt_d, peaks, rz, state_array)
+        out = {
+            "metric": METRIC, "value": world * 1e3 / ms, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{wl}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd",
+                       "views_per_step_per_gpu": 1, "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
+                       "l2": "flushed before every timed step (256 MiB write, outside the events)",
+                       "parallelism": "1 view/GPU, replica per GPU" + (", NCCL all-reduce of 11 floats/Gaussian" if world > 1 else "")},
+            "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
+            "gpu_launches": launches,
+            "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
+            "clocks": clocks, "roofline": roof, "kernels": kern,
+        }
+        if world == 1 and not args.no_cpu:
+            out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def kernel_rooflines(settings, devt, gt_c, gt_d, peaks, rz, state_array, reps=20):
+    """Average duration of each C-ABI stage (CUDA events on the launching stream, L2 flushed) and
+    the roofline of the dominant kernel.  Stage = {geom: memset + preprocess_fwd + tile_scan,
+    render: duplicate + sort_pack(2) + blend_fwd, backward: memset + blend_bwd + preprocess_bwd};
+    the split inside a stage comes from the ncu launch list under profiles/."""
+    from eags_raster import _lib
+    dev = devt["means3D"].device
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    H, W = settings.image_height, settings.image_width
+    dC = torch.sign(torch.randn(3, H, W, device=dev)) / (3 * H * W)
+    dD = torch.sign(torch.randn(1, H, W, device=dev)) / (H * W)
+    tf = tb = 0.0
+    for i in range(reps + 3):
+        flush.zero_()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        out = rz.rasterize_forward(settings, 0, devt["means3D"], devt["opacities"], shs=devt["shs"],
+                                   scales=devt["scales"], rotations=devt["rotations"])
+        e[1].record()
+        st = out[5]
+        flush.zero_()
+        e2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        e2[0].record()
+        rz.rasterize_backward(settings, st, devt["means3D"], devt["opacities"], devt["shs"], None,
+                              devt["scales"], devt["rotations"], None, dC, dD, None, want_shs=False)
+        e2[1].record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            tf += e[0].elapsed_time(e[1])
+            tb += e2[0].elapsed_time(e2[1])
+    tf, tb = tf / reps, tb / reps
+    K = st.num_rendered
+    P = st.P
+    N = H * W
+    ncontrib = state_array(st, "n_contrib").to(torch.int64)
+    ranges = state_array(st, "ranges").to(torch.int64)
+    gx = (W + 15) // 16
+    tile_n = (ranges[:, 1] - ranges[:, 0])
+    ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
+    per_pix_n = tile_n[: ((H + 15) // 16) * gx][(ys // 16) * gx + xs // 16]
+    final_T = state_array(st, "final_T")
+    # S: list entries a pixel iterates before it stops; saturated pixels stop early
+    # (bounded below by their n_contrib), the others walk their whole tile list.
+    S = int(torch.where(final_T * 0.01 < 1e-4, ncontrib, per_pix_n).sum())
+    S_bwd = int(ncontrib.sum())
+    fp32_peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12
+    flops = S * FP32_FLOPS_FWD_PAIR + S_bwd * FP32_FLOPS_BWD_PAIR
+    kern = {
+        "forward_ms": tf, "backward_ms": tb, "K": K, "P": P, "pairs_fwd": S, "pairs_bwd": S_bwd,
+        "algorithmic_bytes": {
+            "preprocess_fwd": P * 128, "duplicate": P * 20 + K * 8, "sort_pack": K * (8 + 40 + 52),
+            "blend_fwd": K * 48 + N * 28, "blend_bwd": K * 48 + N * 28 + K * 40, "preprocess_bwd": P * 250},
+    }
+    roof = {
+        "kernel": "blend_fwd + blend_bwd (FP32-pipe bound; see profiles/ for the per-kernel split)",
+        "bound": "fp32", "achieved": flops / ((tf + tb) * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+        "frac": flops / ((tf + tb) * 1e-3) / 1e12 / fp32_peak, "traffic": None,
+        "peak_source": f"148 SM x 128 lanes x 2 x {peaks['sm_max_mhz']:.0f} MHz (sm clock from MEASURED_PEAKS.json, {peaks['src']})",
+        "hbm": {"bound": "hbm", "achieved": sum(kern["algorithmic_bytes"].values()) / ((tf + tb) * 1e-3) / 1e9,
+                "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": sum(kern["algorithmic_bytes"].values()) / ((tf + tb) * 1e-3) / 1e9 / peaks["hbm_gbs"]},
+    }
+    return roof, kern
+
+
+def oracle_iteration(wl, P=None):
+    """One fwd+bwd of the CPU oracle on the workload; returns a closure (inputs prepared once)."""
+    import numpy as np
+    import oracle
+    from eags_raster import scene
+    sc = scene.make_scene(wl, P=P, seed=0)
+    cam = scene.workload_camera(wl)
+    a = {k: sc[k].numpy() for k in sc}
+    H, W = cam.H, cam.W
+
+    def it():
+        o = oracle.forward(W, H, cam.tanfovx, cam.tanfovy, cam.viewmatrix.numpy(), cam.projmatrix.numpy(),
+                           cam.campos.numpy(), a["means3D"], a["scales"], a["rotations"], a["opacities"], shs=a["shs"])
+        dC = np.sign(o["color"] - a["gt_color"]).astype(np.float32) / (3 * H * W)
+        dD = np.sign(o["depth"] - a["gt_depth"]).astype(np.float32) / (H * W)
+        oracle.backward(o, dC, dD, None)
+    return it, cam, sc["means3D"].shape[0]
+
+
+def cpu_baseline(wl, budget_s=15.0):
+    import oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    oracle.set_num_threads(cores)
+    it, cam, P = oracle_iteration(wl)
+    it()   # warm-up (page faults, OpenMP pool)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        it()
+        n += 1
+        el = time.perf_counter() - t0
+        if el > budget_s or n >= 20:
+            break
+    return {"value": n / el, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+            "sample": f"{n} full fwd+bwd iterations of {wl} ({cam.W}x{cam.H}, {P} Gaussians) with the C oracle (OpenMP)"}
+
+
+def run_reference(args):
+    """The reference arm: the reference's CUDA kernels are un-vendored pip packages and it has no
+    CPU implementation of this path, so this times the CPU oracle port on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    oracle.set_num_threads(cores)
+    it, cam, P = oracle_iteration(args.workload)
+    steps = min(args.steps, 10)
+    for _ in range(min(max(args.warmup, 1), 2)):
+        it()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        it()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    v = 1e3 / ms
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(max(args.warmup, 1), 2), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+                         "sample": f"{steps} full fwd+bwd iterations per run (one iteration per step)"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sync-mode", default=None, choices=["optimistic", "exact", "nosync"])
+    ap.add_argument("--tma", type=int, default=None)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    from eags_raster import _lib, rasterize as rz
+    if args.sync_mode:
+        rz.set_sync_mode(args.sync_mode)
+    if args.tma is not None:
+        _lib.set_option("tma", args.tma)
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
