@@ -34,7 +34,7 @@ tile_scan_kernel(ImagePtrs img) {
     __syncthreads();
     for (int base = 0; base < img.G; base += SCAN_THREADS) {
         const int t = base + tid;
-        const unsigned c = (t < img.G) ? img.tile_count[t] : 0u;
+        const unsigned c = (t < img.G) ? img.tile_count[(size_t)t * EAGS_CTR_STRIDE] : 0u;
         unsigned incl = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -58,7 +58,7 @@ tile_scan_kernel(ImagePtrs img) {
         const unsigned start = carry + s_warp[warp] + incl - c;
         if (t < img.G) {
             img.ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
-            img.tile_cursor[t] = start;
+            img.tile_count[(size_t)t * EAGS_CTR_STRIDE] = start;   // the counter becomes the scatter cursor
             img.tile_max[t] = 0u;
             if (c > EAGS_SORT_SMALL_CAP) {
                 unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
@@ -75,24 +75,118 @@ tile_scan_kernel(ImagePtrs img) {
 // ------------------------------------------------------------------------------------------------
 // K4: per-tile sort + pack
 // ------------------------------------------------------------------------------------------------
-// Bitonic network in its "flip" form: every compare-exchange is ascending, so a partner index
-// >= n behaves like a +inf pad that never moves and n need not be a power of two.
-// Sync elision: with c = tid + m*THREADS, the 32 compare-exchanges of one warp iteration touch one
-// aligned 64-element window whenever the stage span is <= 64, so consecutive stages with
-// span <= 64 only need __syncwarp().
+// Bitonic network in its "flip" form: every compare-exchange is ascending, so +inf pads at the top
+// indices never move and n need not be a power of two.
+//
+// Shared-memory bandwidth is what bounds a per-tile sort (8 CTAs/SM x 55 stages x 16 KB), so the
+// network is split: every stage whose span fits a 64-key window (45 of the 55 stages at 1 024 keys)
+// runs in REGISTERS -- a warp holds a window as two keys per lane and exchanges with shuffles -- and
+// only the stages with span > 64 go through shared memory.
+typedef unsigned long long u64;
+
+__device__ __forceinline__ u64 shfl_xor64(u64 v, int m) {
+    return __shfl_xor_sync(0xffffffffu, v, m);
+}
+__device__ __forceinline__ void cex_lane(u64& e, int lane, int m, bool keep_min) {
+    const u64 o = shfl_xor64(e, m);
+    e = keep_min ? (o < e ? o : e) : (o > e ? o : e);
+    (void)lane;
+}
+// regular stages j = 32, 16, ..., 1 on a 64-key window (e0 = key[lane], e1 = key[lane + 32])
+__device__ __forceinline__ void window_merge(u64& e0, u64& e1, int lane) {
+    if (e0 > e1) { const u64 t = e0; e0 = e1; e1 = t; }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const bool lo = (lane & j) == 0;
+        cex_lane(e0, lane, j, lo);
+        cex_lane(e1, lane, j, lo);
+    }
+}
+// full sort of a 64-key window: k = 2 .. 64
+__device__ __forceinline__ void window_sort(u64& e0, u64& e1, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+        // flip: i <-> i ^ (k - 1); the key whose bit k/2 is clear keeps the minimum
+        const bool lo = (lane & (k >> 1)) == 0;
+        cex_lane(e0, lane, k - 1, lo);
+        cex_lane(e1, lane, k - 1, lo);
+#pragma unroll
+        for (int j = k >> 2; j > 0; j >>= 1) {
+            const bool l2 = (lane & j) == 0;
+            cex_lane(e0, lane, j, l2);
+            cex_lane(e1, lane, j, l2);
+        }
+    }
+    // k = 64 flip: key[l] <-> key[63 - l], i.e. e0 of lane l with e1 of lane 31 - l
+    {
+        const u64 o1 = shfl_xor64(e1, 31), o0 = shfl_xor64(e0, 31);
+        e0 = o1 < e0 ? o1 : e0;
+        e1 = o0 > e1 ? o0 : e1;
+    }
+    // then regular stages j = 16 .. 1 inside each half (j = 32 is not part of the k = 64 merge
+    // after the flip: the flip itself is the span-64 stage)
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const bool lo = (lane & j) == 0;
+        cex_lane(e0, lane, j, lo);
+        cex_lane(e1, lane, j, lo);
+    }
+}
+
+// s[0 .. npad) holds the keys, +inf padded; npad is a power of two >= 64.
 template <int THREADS>
-__device__ __forceinline__ void bitonic_sort(unsigned long long* s, int n, bool warp_sync_ok) {
+__device__ __forceinline__ void bitonic_sort_hybrid(u64* s, int npad) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NW = THREADS / 32;
+    const int nwin = npad >> 6;
+    __syncthreads();
+    for (int w = warp; w < nwin; w += NW) {
+        u64 e0 = s[w * 64 + lane], e1 = s[w * 64 + lane + 32];
+        window_sort(e0, e1, lane);
+        s[w * 64 + lane] = e0;
+        s[w * 64 + lane + 32] = e1;
+    }
+    const int half = npad >> 1;
+    for (int k = 128; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j >= 64; j >>= 1) {
+            __syncthreads();
+            const bool flip = (j == (k >> 1));
+            for (int c = threadIdx.x; c < half; c += THREADS) {
+                int i, p;
+                if (flip) {
+                    const int blk = c / j, off = c - blk * j;
+                    i = blk * k + off;
+                    p = blk * k + (k - 1 - off);
+                } else {
+                    i = 2 * c - (c & (j - 1));
+                    p = i + j;
+                }
+                const u64 a = s[i], b = s[p];
+                if (a > b) { s[i] = b; s[p] = a; }
+            }
+        }
+        __syncthreads();
+        for (int w = warp; w < nwin; w += NW) {
+            u64 e0 = s[w * 64 + lane], e1 = s[w * 64 + lane + 32];
+            window_merge(e0, e1, lane);
+            s[w * 64 + lane] = e0;
+            s[w * 64 + lane + 32] = e1;
+        }
+    }
+    __syncthreads();
+}
+
+// Generic (global-memory capable) variant for lists beyond the shared-memory capacity: partner
+// indices >= n are skipped instead of padded.
+template <int THREADS>
+__device__ __forceinline__ void bitonic_sort_generic(u64* s, int n) {
     int npad = 2;
     while (npad < n) npad <<= 1;
     const int half = npad >> 1;
-    int prev_span = 1 << 30;   // force a block barrier before the first stage
     for (int k = 2; k <= npad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             const bool flip = (j == (k >> 1));
-            const int span = flip ? k : (j << 1);
-            if (warp_sync_ok && prev_span <= 64 && span <= 64) __syncwarp();
-            else __syncthreads();
-            prev_span = span;
+            __syncthreads();
             for (int c = threadIdx.x; c < half; c += THREADS) {
                 int i, p;
                 if (flip) {
@@ -104,13 +198,21 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* s, int n, bool 
                     p = i + j;
                 }
                 if (p < n) {
-                    const unsigned long long a = s[i], b = s[p];
+                    const u64 a = s[i], b = s[p];
                     if (a > b) { s[i] = b; s[p] = a; }
                 }
             }
         }
     }
     __syncthreads();
+}
+
+template <int THREADS>
+__device__ __forceinline__ void load_and_sort(u64* s, const u64* __restrict__ src, int n) {
+    int npad = 64;
+    while (npad < n) npad <<= 1;
+    for (int k = threadIdx.x; k < npad; k += THREADS) s[k] = k < n ? src[k] : ~0ull;
+    bitonic_sort_hybrid<THREADS>(s, npad);
 }
 
 struct PackArgs {
@@ -133,9 +235,11 @@ __device__ __forceinline__ void pack_sorted(const unsigned long long* s, int n, 
         const float4 cd = a.rgbd[idx];
         const size_t o = (size_t)start + k;
         a.point_list[o] = idx;
+        // log2-scaled conic and the alpha >= 1/255 reach (blend.cu: record format)
+        const float L = 1.4426950408889634f;
         a.records[3 * o + 0] = make_float4(xy.x, xy.y, __uint_as_float(idx), cd.w);
-        a.records[3 * o + 1] = co;
-        a.records[3 * o + 2] = make_float4(cd.x, cd.y, cd.z, 0.f);
+        a.records[3 * o + 1] = make_float4(-0.5f * L * co.x, -L * co.y, -0.5f * L * co.z, co.w);
+        a.records[3 * o + 2] = make_float4(cd.x, cd.y, cd.z, __log2f(255.f * co.w));
         if (a.keys) a.keys[o] = ((unsigned long long)tile << 32) | (key >> 32);
     }
 }
@@ -149,9 +253,7 @@ sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ uns
     const uint2 rg = img.ranges[tile];
     const int n = (int)(rg.y - rg.x);
     if (n <= 0 || n > EAGS_SORT_SMALL_CAP) return;
-    for (int k = threadIdx.x; k < n; k += 256) s_keys[k] = unsorted[(size_t)rg.x + k];
-    if (n > 1) bitonic_sort<256>(s_keys, n, true);
-    else __syncthreads();
+    load_and_sort<256>(s_keys, unsorted + (size_t)rg.x, n);
     pack_sorted<256>(s_keys, n, rg.x, tile, a);
 }
 
@@ -167,12 +269,11 @@ sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, l
         const int n = (int)(rg.y - rg.x);
         if (n <= EAGS_SORT_BIG_CAP) {
             __syncthreads();   // previous tile's pack has finished reading s_big
-            for (int k = threadIdx.x; k < n; k += 1024) s_big[k] = unsorted[(size_t)rg.x + k];
-            bitonic_sort<1024>(s_big, n, true);
+            load_and_sort<1024>(s_big, unsorted + (size_t)rg.x, n);
             pack_sorted<1024>(s_big, n, rg.x, tile, a);
         } else {
             unsigned long long* g = unsorted + (size_t)rg.x;   // in place, in global memory
-            bitonic_sort<1024>(g, n, false);
+            bitonic_sort_generic<1024>(g, n);
             pack_sorted<1024>(g, n, rg.x, tile, a);
         }
     }

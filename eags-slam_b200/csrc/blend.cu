@@ -62,11 +62,53 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     } while (!done);
 }
 
+// ---- splat records (written by sort_pack, binning.cu) ---------------------------------------------
+//   R0 = {x, y, bits(gaussian index), depth}
+//   R1 = {A, B, C, opacity}   with  log2(G) = A dx^2 + B dx dy + C dy^2,
+//                                   A = -0.5 log2(e) conic.xx, B = -log2(e) conic.xy, C = -0.5 log2(e) conic.yy
+//   R2 = {r, g, b, tau2}      tau2 = log2(255 opacity): the splat reaches alpha >= 1/255 iff -log2(G) <= tau2
+constexpr float LN2 = 0.6931471805599453f;
+__device__ __forceinline__ float fast_exp2(float x) {   // MUFU.EX2, 2 ulp, flushes to 0 below 2^-126
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+constexpr float CULL_MARGIN = 0.02f;   // log2 units (1.4 %) >> any fp32 rounding of the pixel test
+
+// Warp w owns the 8x4 pixel block at (8 (w & 1), 4 (w >> 1)) of the 16x16 tile; lane l -> (l & 7, l >> 3).
+__device__ __forceinline__ void warp_region(int tile, int gx, int warp, int lane, int& px, int& py,
+                                            float& rx0, float& ry0) {
+    const int tx = tile % gx, ty = tile / gx;
+    const int ox = tx * EAGS_TILE + (warp & 1) * 8, oy = ty * EAGS_TILE + (warp >> 1) * 4;
+    px = ox + (lane & 7);
+    py = oy + (lane >> 3);
+    rx0 = (float)ox;
+    ry0 = (float)oy;
+}
+
+// Conservative, exact-arithmetic-independent cull: can the splat reach alpha >= 1/255 anywhere in the
+// continuous rectangle [rx0, rx0+7] x [ry0, ry0+3]?  q(d) = -log2 G(d) is a convex quadratic; its
+// minimum over the rectangle is 0 if the mean is inside, else it lies on an edge facing the mean,
+// where the 1-D minimiser is a clamp.  Non-positive-definite conics are never culled.
+__device__ __forceinline__ bool splat_may_touch(const float4 r0, const float4 r1, float tau2, float rx0,
+                                                float ry0) {
+    const float a2 = -2.f * r1.x, b2 = -r1.y, c2 = -2.f * r1.z;
+    const float lx = rx0 - r0.x, ux = lx + 7.f, ly = ry0 - r0.y, uy = ly + 3.f;
+    const float ex = fminf(fmaxf(0.f, lx), ux), ey = fminf(fmaxf(0.f, ly), uy);
+    const float dy1 = fminf(fmaxf(__fdividef(-b2 * ex, c2), ly), uy);
+    const float q1 = 0.5f * a2 * ex * ex + b2 * ex * dy1 + 0.5f * c2 * dy1 * dy1;
+    const float dx2 = fminf(fmaxf(__fdividef(-b2 * ey, a2), lx), ux);
+    const float q2 = 0.5f * a2 * dx2 * dx2 + b2 * dx2 * ey + 0.5f * c2 * ey * ey;
+    const bool pd = a2 > 0.f && c2 > 0.f && a2 * c2 - b2 * b2 > 0.f;
+    return !(pd && fminf(q1, q2) > tau2 + CULL_MARGIN);
+}
+
 // ================================================================================================
 // K6  blend forward
 // ================================================================================================
 constexpr int FWD_BATCH = 128;   // records per stage (6 KB)
 constexpr int FWD_STAGES = 3;
+constexpr int FWD_ROUNDS = FWD_BATCH / 32;
 
 struct FwdArgs {
     int W, H, gx;
@@ -93,16 +135,18 @@ blend_fwd_kernel(FwdArgs a) {
     __shared__ unsigned s_max;
 
     if (a.ctrl->num_rendered > (unsigned long long)a.capacity) return;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
-    const int tx = tile % a.gx, ty = tile / a.gx;
     const uint2 rg = a.ranges[tile];
     const int n = (int)(rg.y - rg.x);
-    const int px = tx * EAGS_TILE + (tid & 15), py = ty * EAGS_TILE + (tid >> 4);
+    int px, py;
+    float rx0, ry0;
+    warp_region(tile, a.gx, warp, lane, px, py, rx0, ry0);
     const bool inside = px < a.W && py < a.H;
     const float pxf = (float)px, pyf = (float)py;
     const float4* src = a.records + (size_t)3 * rg.x;
     const int nb = (n + FWD_BATCH - 1) / FWD_BATCH;
+    const bool count_touched = VARIANT_B && a.n_touched != nullptr;
 
     if (tid == 0) {
         s_max = 0;
@@ -123,7 +167,6 @@ blend_fwd_kernel(FwdArgs a) {
 
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
     unsigned last = 0;
-    const bool count_touched = VARIANT_B && a.n_touched != nullptr;
     bool done = !inside;
 
     for (int b = 0; b < nb; b++) {
@@ -133,32 +176,48 @@ blend_fwd_kernel(FwdArgs a) {
         if (TMA) {
             stage = b % FWD_STAGES;
             mbar_wait(&s_bar[stage], (uint32_t)((b / FWD_STAGES) & 1));
+            __syncwarp();   // the try_wait loop exits per thread: reconverge before the warp-wide code
         } else {
             stage = 0;
             for (int k = tid; k < cnt * 3; k += BLK) s_rec[0][k] = src[(size_t)3 * base + k];
             __syncthreads();
         }
-        if (!done) {
-            const float4* rec = s_rec[stage];
-            for (int j = 0; j < cnt; j++) {
-                const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
-                const float dx = r0.x - pxf, dy = r0.y - pyf;
-                const float power = -0.5f * (r1.x * dx * dx + r1.z * dy * dy) - r1.y * dx * dy;
-                if (power > 0.f) continue;
-                const float alpha = fminf(0.99f, r1.w * __expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = T * (1.f - alpha);
-                if (test_T < 0.0001f) { done = true; break; }
-                const float4 r2 = rec[3 * j + 2];
-                const float w = alpha * T;
-                C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
-                D += r0.w * w;
-                A += w;
-                if (VARIANT_B) {
-                    if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+        const float4* rec = s_rec[stage];
+        if (!__all_sync(FULL, done)) {
+            // pass 1: one splat per lane -> bitmask of the splats that can touch this warp's 8x4 block
+            unsigned mask[FWD_ROUNDS];
+#pragma unroll
+            for (int r = 0; r < FWD_ROUNDS; r++) {
+                const int jj = r * 32 + lane;
+                bool keep = false;
+                if (jj < cnt) keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
+                mask[r] = __ballot_sync(FULL, keep);
+            }
+            // pass 2: front-to-back over the survivors (warp-uniform loop, per-lane predicates)
+#pragma unroll
+            for (int r = 0; r < FWD_ROUNDS; r++) {
+                unsigned m = mask[r];
+                while (m) {
+                    const int j = r * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+                    const float dx = r0.x - pxf, dy = r0.y - pyf;
+                    const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
+                    const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
+                    if (done || power2 > 0.f || alpha < 1.0f / 255.0f) continue;
+                    const float test_T = T * (1.f - alpha);
+                    if (test_T < 0.0001f) { done = true; continue; }
+                    const float4 r2 = rec[3 * j + 2];
+                    const float w = alpha * T;
+                    C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
+                    D += r0.w * w;
+                    A += w;
+                    if (VARIANT_B) {
+                        if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                    }
+                    T = test_T;
+                    last = (unsigned)(base + j + 1);
                 }
-                T = test_T;
-                last = (unsigned)(base + j + 1);
             }
         }
         const int ndone = __syncthreads_count(done ? 1 : 0);
@@ -166,7 +225,7 @@ blend_fwd_kernel(FwdArgs a) {
             if (tid < cnt) {
                 const int v = s_touched[tid];
                 if (v) {
-                    atomicAdd(&a.n_touched[__float_as_uint(s_rec[stage][3 * tid].z)], v);
+                    atomicAdd(&a.n_touched[__float_as_uint(rec[3 * tid].z)], v);
                     s_touched[tid] = 0;
                 }
             }
@@ -185,6 +244,7 @@ blend_fwd_kernel(FwdArgs a) {
             tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
         }
     }
+    __syncwarp();
 
     if (inside) {
         const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
@@ -197,7 +257,7 @@ blend_fwd_kernel(FwdArgs a) {
         a.out_third[pix] = VARIANT_B ? 1.f - T : A;
     }
     const unsigned m = __reduce_max_sync(FULL, last);
-    if ((tid & 31) == 0 && m) atomicMax(&s_max, m);
+    if (lane == 0 && m) atomicMax(&s_max, m);
     __syncthreads();
     if (tid == 0) a.tile_max[tile] = s_max;
 }
@@ -207,6 +267,7 @@ blend_fwd_kernel(FwdArgs a) {
 // ================================================================================================
 constexpr int BWD_BATCH = 64;    // records per stage (3 KB); also the width of the per-warp bitmask
 constexpr int BWD_STAGES = 3;
+constexpr int BWD_ROUNDS = BWD_BATCH / 32;
 constexpr int PART_STRIDE = 11;  // 10 components + 1 pad: conflict-free column reads in the flush
 
 struct BwdArgs {
@@ -274,8 +335,9 @@ blend_bwd_kernel(BwdArgs a) {
     const uint2 rg = a.ranges[tile];
     const int n = min((int)(rg.y - rg.x), (int)a.tile_max[tile]);   // nothing past max n_contrib matters
     if (n <= 0) return;
-    const int tx = tile % a.gx, ty = tile / a.gx;
-    const int px = tx * EAGS_TILE + (tid & 15), py = ty * EAGS_TILE + (tid >> 4);
+    int px, py;
+    float rx0, ry0;
+    warp_region(tile, a.gx, warp, lane, px, py, rx0, ry0);
     const bool inside = px < a.W && py < a.H;
     const float pxf = (float)px, pyf = (float)py;
     const float4* src = a.records + (size_t)3 * rg.x;
@@ -308,6 +370,7 @@ blend_bwd_kernel(BwdArgs a) {
         dD = a.dL_ddepth[pix];
         dA = a.dL_dthird ? a.dL_dthird[pix] : 0.f;
     }
+    const int warp_last = __reduce_max_sync(FULL, last_contributor);
     float T = T_final;
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc_d = 0.f, acc_a = 0.f;
     float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
@@ -321,6 +384,7 @@ blend_bwd_kernel(BwdArgs a) {
         if (TMA) {
             stage = bi % BWD_STAGES;
             mbar_wait(&s_bar[stage], (uint32_t)((bi / BWD_STAGES) & 1));
+            __syncwarp();
         } else {
             stage = 0;
             if (tid < cnt * 3) s_rec[0][tid] = src[(size_t)3 * base + tid];
@@ -328,53 +392,75 @@ blend_bwd_kernel(BwdArgs a) {
         }
         const float4* rec = s_rec[stage];
         unsigned long long wrote = 0ull;
-        for (int j = cnt - 1; j >= 0; j--) {
-            const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
-            const float dx = r0.x - pxf, dy = r0.y - pyf;
-            const float power = -0.5f * (r1.x * dx * dx + r1.z * dy * dy) - r1.y * dx * dy;
-            const float G = __expf(power);
-            const float alpha = fminf(0.99f, r1.w * G);
-            const bool active = inside && (base + j < last_contributor) && (power <= 0.f) &&
-                                (alpha >= 1.0f / 255.0f);
-            if (!__any_sync(FULL, active)) continue;   // warp-uniform
-            float v[10];
+        if (base < warp_last) {
+            // pass 1: cull against this warp's 8x4 block and its deepest contributor
+            unsigned mask[BWD_ROUNDS];
 #pragma unroll
-            for (int k = 0; k < 10; k++) v[k] = 0.f;
-            if (active) {
-                const float4 r2 = rec[3 * j + 2];
-                const float inv1ma = __fdividef(1.f, 1.f - alpha);
-                T = T * inv1ma;
-                const float w = alpha * T;
-                float dL_dalpha;
-                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = r2.x;
-                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = r2.y;
-                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = r2.z;
-                dL_dalpha = (r2.x - acc0) * dC0 + (r2.y - acc1) * dC1 + (r2.z - acc2) * dC2;
-                v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2;
-                acc_d = last_alpha * last_depth + (1.f - last_alpha) * acc_d; last_depth = r0.w;
-                dL_dalpha += (r0.w - acc_d) * dD;
-                v[9] = w * dD;
-                acc_a = last_alpha + (1.f - last_alpha) * acc_a;
-                dL_dalpha += (1.f - acc_a) * dA;
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final * inv1ma) * bg_dot;
-                const float dL_dG = r1.w * dL_dalpha;   // Q1: the 0.99 clamp is straight-through
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
-                const float dG_ddely = -gdy * r1.z - gdx * r1.y;
-                v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                v[1] = dL_dG * dG_ddely * ddely_dy;
-                v[2] = -0.5f * gdx * dx * dL_dG;
-                v[3] = -0.5f * gdx * dy * dL_dG;   // Q8: half the true off-diagonal derivative
-                v[4] = -0.5f * gdy * dy * dL_dG;
-                v[5] = G * dL_dalpha;
+            for (int r = 0; r < BWD_ROUNDS; r++) {
+                const int jj = r * 32 + lane;
+                bool keep = false;
+                if (jj < cnt && base + jj < warp_last)
+                    keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
+                mask[r] = __ballot_sync(FULL, keep);
             }
-            int slot;
-            bool valid;
-            const float tot = butterfly10(v, lane, slot, valid);
-            if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
-            wrote |= 1ull << j;
+            // pass 2: back-to-front over the survivors
+#pragma unroll
+            for (int r = BWD_ROUNDS - 1; r >= 0; r--) {
+                unsigned m = mask[r];
+                while (m) {
+                    const int bit = 31 - __clz(m);
+                    m &= ~(1u << bit);
+                    const int j = r * 32 + bit;
+                    const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+                    const float dx = r0.x - pxf, dy = r0.y - pyf;
+                    const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
+                    const float G = fast_exp2(power2);
+                    const float alpha = fminf(0.99f, r1.w * G);
+                    const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
+                                        (alpha >= 1.0f / 255.0f);
+                    if (!__any_sync(FULL, active)) continue;   // warp-uniform
+                    float v[10];
+#pragma unroll
+                    for (int k = 0; k < 10; k++) v[k] = 0.f;
+                    if (active) {
+                        const float4 r2 = rec[3 * j + 2];
+                        const float inv1ma = __fdividef(1.f, 1.f - alpha);
+                        T = T * inv1ma;
+                        const float w = alpha * T;
+                        float dL_dalpha;
+                        acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = r2.x;
+                        acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = r2.y;
+                        acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = r2.z;
+                        dL_dalpha = (r2.x - acc0) * dC0 + (r2.y - acc1) * dC1 + (r2.z - acc2) * dC2;
+                        v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2;
+                        acc_d = last_alpha * last_depth + (1.f - last_alpha) * acc_d; last_depth = r0.w;
+                        dL_dalpha += (r0.w - acc_d) * dD;
+                        v[9] = w * dD;
+                        acc_a = last_alpha + (1.f - last_alpha) * acc_a;
+                        dL_dalpha += (1.f - acc_a) * dA;
+                        dL_dalpha *= T;
+                        last_alpha = alpha;
+                        dL_dalpha += (-T_final * inv1ma) * bg_dot;
+                        const float dL_dG = r1.w * dL_dalpha;   // Q1: the 0.99 clamp is straight-through
+                        const float gdx = G * dx, gdy = G * dy;
+                        // true conic from the log2-scaled record: xx = -2 ln2 A, xy = -ln2 B, yy = -2 ln2 C
+                        const float cxx = -2.f * LN2 * r1.x, cxy = -LN2 * r1.y, cyy = -2.f * LN2 * r1.z;
+                        const float dG_ddelx = -gdx * cxx - gdy * cxy;
+                        const float dG_ddely = -gdy * cyy - gdx * cxy;
+                        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                        v[1] = dL_dG * dG_ddely * ddely_dy;
+                        v[2] = -0.5f * gdx * dx * dL_dG;
+                        v[3] = -0.5f * gdx * dy * dL_dG;   // Q8: half the true off-diagonal derivative
+                        v[4] = -0.5f * gdy * dy * dL_dG;
+                        v[5] = G * dL_dalpha;
+                    }
+                    int slot;
+                    bool valid;
+                    const float tot = butterfly10(v, lane, slot, valid);
+                    if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
+                    wrote |= 1ull << j;
+                }
+            }
         }
         if (lane == 0) s_mask[warp] = wrote;
         __syncthreads();

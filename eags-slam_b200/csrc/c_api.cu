@@ -86,7 +86,7 @@ int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_s
     ImagePtrs img = image_ptrs(image_state, W, H);
     GeomPtrs geom = geom_ptrs(geom_state, g->P);
     // ctrl + tile_count are contiguous: one memset node
-    CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4, s), "memset(ctrl)");
+    CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4 * EAGS_CTR_STRIDE, s), "memset(ctrl)");
     CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, s), "preprocess_fwd");
     CHECK_LAUNCH(launch_tile_scan(img, s), "tile_scan");
     if (num_rendered_pinned)
@@ -163,7 +163,7 @@ int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t c
         {"tiles_touched", gb, GL.tiles_touched, P, 4},
         {"clamped", gb, GL.clamped, P, 1},
         {"ctrl", ib, IL.ctrl, 1, 64},
-        {"tile_count", ib, IL.tile_count, IL.G, 4},
+        {"tile_count", ib, IL.tile_count, (int64_t)IL.G * EAGS_CTR_STRIDE, 4},
         {"ranges", ib, IL.ranges, IL.G, 8},
         {"tile_max_contrib", ib, IL.tile_max, IL.G, 4},
         {"final_T", ib, IL.final_T, IL.N, 4},

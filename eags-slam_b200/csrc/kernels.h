@@ -16,7 +16,6 @@ struct GeomPtrs {
 struct ImagePtrs {
     EagsCtrl* ctrl;
     uint32_t* tile_count;
-    uint32_t* tile_cursor;
     uint2* ranges;
     uint32_t* big_list;
     uint32_t* tile_max;
@@ -49,7 +48,6 @@ static inline ImagePtrs image_ptrs(void* base, int W, int H) {
     ImagePtrs p;
     p.ctrl = (EagsCtrl*)(b + L.ctrl);
     p.tile_count = (uint32_t*)(b + L.tile_count);
-    p.tile_cursor = (uint32_t*)(b + L.tile_cursor);
     p.ranges = (uint2*)(b + L.ranges);
     p.big_list = (uint32_t*)(b + L.big_list);
     p.tile_max = (uint32_t*)(b + L.tile_max);

@@ -12,8 +12,9 @@
 //
 //   image state  (per tile / per pixel)
 //     ctrl          Ctrl        counters, zeroed at the start of every forward
-//     tile_count    u32[G]      keys per tile (zeroed with ctrl; atomics in preprocess_fwd)
-//     tile_cursor   u32[G]      scatter cursor (tile_scan -> duplicate)
+//     tile_count    u32[G*32]   keys per tile, one counter per 128-byte line (zeroed with ctrl; RED
+//                               atomics in preprocess_fwd); tile_scan turns it into the scatter
+//                               cursor that duplicate advances with ATOM
 //     ranges        uint2[G]    [start, end) of each tile in the sorted list
 //     big_list      u32[G]      tiles whose list does not fit the small sort CTA
 //     tile_max      u32[G]      max n_contrib over the tile's pixels (bounds the backward walk)
@@ -31,6 +32,8 @@
 #include <stdint.h>
 
 #define EAGS_TILE 16
+#define EAGS_CTR_STRIDE 32          // per-tile counters live one per 128-byte line: the L2 atomic unit
+                                   // serialises RED/ATOM traffic per line, 38 hot lines cost 60 us at c2
 #define EAGS_SORT_SMALL_CAP 2048   // keys a 256-thread sort CTA holds in shared memory
 #define EAGS_SORT_BIG_CAP 16384    // keys a 1024-thread sort CTA holds in shared memory
 
@@ -60,7 +63,7 @@ static inline GeomLayout geom_layout(int64_t P) {
 }
 
 struct ImageLayout {
-    size_t ctrl, tile_count, tile_cursor, ranges, big_list, tile_max, final_T, n_contrib, total;
+    size_t ctrl, tile_count, ranges, big_list, tile_max, final_T, n_contrib, total;
     int gx, gy, G;
     int64_t N;
 };
@@ -72,8 +75,7 @@ static inline ImageLayout image_layout(int W, int H) {
     L.N = (int64_t)W * H;
     size_t o = 0;
     L.ctrl = o;        o += 64;
-    L.tile_count = o;  o += eags_align256((size_t)L.G * 4 + 64) - 64;   // ctrl + tile_count: one memset
-    L.tile_cursor = o; o += eags_align256((size_t)L.G * 4);
+    L.tile_count = o;  o += eags_align256((size_t)L.G * 4 * EAGS_CTR_STRIDE + 64) - 64;   // ctrl + counters: one memset
     L.ranges = o;      o += eags_align256((size_t)L.G * 8);
     L.big_list = o;    o += eags_align256((size_t)L.G * 4);
     L.tile_max = o;    o += eags_align256((size_t)L.G * 4);

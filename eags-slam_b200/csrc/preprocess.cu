@@ -265,7 +265,7 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
             my_tiles = (unsigned)((x1 - x0) * (y1 - y0));
             // per-tile key counts: no-return RED atomics spread over G addresses
             for (int y = y0; y < y1; y++)
-                for (int x = x0; x < x1; x++) atomicAdd(&tile_count[y * a.gx + x], 1u);
+                for (int x = x0; x < x1; x++) atomicAdd(&tile_count[(size_t)(y * a.gx + x) * EAGS_CTR_STRIDE], 1u);
         } while (0);
         radii[i] = r_out;
         geom.tiles_touched[i] = my_tiles;
@@ -298,7 +298,7 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, GeomP
     const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
     for (int y = y0; y < y1; y++)
         for (int x = x0; x < x1; x++) {
-            unsigned slot = atomicAdd(&tile_cursor[y * gx + x], 1u);
+            unsigned slot = atomicAdd(&tile_cursor[(size_t)(y * gx + x) * EAGS_CTR_STRIDE], 1u);
             unsorted[slot] = key;
         }
 }
@@ -656,7 +656,7 @@ int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs ge
     (void)v;
     if (P <= 0) return 0;
     duplicate_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(
-        P, img.gx, img.gy, radii, geom, img.tile_cursor, img.ctrl, bin.unsorted, bin.capacity);
+        P, img.gx, img.gy, radii, geom, img.tile_count, img.ctrl, bin.unsorted, bin.capacity);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
