@@ -24,7 +24,9 @@
 
 namespace {
 
-constexpr int BLK = 256;
+constexpr int BLK = 128;          // 4 warps = one 16x8 half tile per work unit
+constexpr int WARPS = BLK / 32;
+constexpr int UNITS_PER_TILE = 8 / WARPS;
 constexpr unsigned FULL = 0xffffffffu;
 
 // ---- mbarrier / TMA bulk-copy helpers (PTX) ------------------------------------------------------
@@ -68,6 +70,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 //                                   A = -0.5 log2(e) conic.xx, B = -log2(e) conic.xy, C = -0.5 log2(e) conic.yy
 //   R2 = {r, g, b, tau2}      tau2 = log2(255 opacity): the splat reaches alpha >= 1/255 iff -log2(G) <= tau2
 constexpr float LN2 = 0.6931471805599453f;
+__device__ __forceinline__ float fast_rcp(float x) {    // MUFU.RCP, 1 ulp
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ float fast_exp2(float x) {   // MUFU.EX2, 2 ulp, flushes to 0 below 2^-126
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -75,11 +82,12 @@ __device__ __forceinline__ float fast_exp2(float x) {   // MUFU.EX2, 2 ulp, flus
 }
 constexpr float CULL_MARGIN = 0.02f;   // log2 units (1.4 %) >> any fp32 rounding of the pixel test
 
-// Warp w owns the 8x4 pixel block at (8 (w & 1), 4 (w >> 1)) of the 16x16 tile; lane l -> (l & 7, l >> 3).
-__device__ __forceinline__ void warp_region(int tile, int gx, int warp, int lane, int& px, int& py,
+// A 16x16 tile is eight 8x4 pixel blocks; block s sits at (8 (s & 1), 4 (s >> 1)); lane l -> (l & 7, l >> 3).
+// A work unit is half a tile: warp w of the CTA owns block s = 4 * half + w.
+__device__ __forceinline__ void warp_region(int tile, int gx, int sub, int lane, int& px, int& py,
                                             float& rx0, float& ry0) {
     const int tx = tile % gx, ty = tile / gx;
-    const int ox = tx * EAGS_TILE + (warp & 1) * 8, oy = ty * EAGS_TILE + (warp >> 1) * 4;
+    const int ox = tx * EAGS_TILE + (sub & 1) * 8, oy = ty * EAGS_TILE + (sub >> 1) * 4;
     px = ox + (lane & 7);
     py = oy + (lane >> 3);
     rx0 = (float)ox;
@@ -106,13 +114,17 @@ __device__ __forceinline__ bool splat_may_touch(const float4 r0, const float4 r1
 // ================================================================================================
 // K6  blend forward
 // ================================================================================================
+// Persistent CTAs pull half-tile work units from an atomic queue: no wave quantisation (1 200 tiles
+// on 148 SMs x 6 resident 256-thread CTAs was 1.35 waves = 2 rounds) and the tail is at most one
+// half tile long.  The mbarrier ring keeps running across units (`it` = batches issued so far).
 constexpr int FWD_BATCH = 128;   // records per stage (6 KB)
 constexpr int FWD_STAGES = 3;
 constexpr int FWD_ROUNDS = FWD_BATCH / 32;
 
 struct FwdArgs {
-    int W, H, gx;
+    int W, H, gx, n_units;
     const EagsCtrl* ctrl;
+    unsigned* work;
     long long capacity;
     const uint2* ranges;
     const float4* records;
@@ -132,134 +144,141 @@ blend_fwd_kernel(FwdArgs a) {
     __shared__ __align__(128) float4 s_rec[FWD_STAGES][FWD_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[FWD_STAGES];
     __shared__ int s_touched[VARIANT_B ? FWD_BATCH : 1];
-    __shared__ unsigned s_max;
+    __shared__ int s_unit;
 
     if (a.ctrl->num_rendered > (unsigned long long)a.capacity) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
-    const uint2 rg = a.ranges[tile];
-    const int n = (int)(rg.y - rg.x);
-    int px, py;
-    float rx0, ry0;
-    warp_region(tile, a.gx, warp, lane, px, py, rx0, ry0);
-    const bool inside = px < a.W && py < a.H;
-    const float pxf = (float)px, pyf = (float)py;
-    const float4* src = a.records + (size_t)3 * rg.x;
-    const int nb = (n + FWD_BATCH - 1) / FWD_BATCH;
     const bool count_touched = VARIANT_B && a.n_touched != nullptr;
-
-    if (tid == 0) {
-        s_max = 0;
-        if (TMA) {
-            for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_bar[s], 1);
-            mbar_fence_init();
-        }
-    }
-    if (VARIANT_B && tid < FWD_BATCH) s_touched[tid] = 0;
-    __syncthreads();
     if (TMA && tid == 0) {
-        for (int b = 0; b < FWD_STAGES && b < nb; b++) {
-            const int cnt = min(FWD_BATCH, n - b * FWD_BATCH);
-            mbar_expect_tx(&s_bar[b], (uint32_t)cnt * 48u);
-            tma_bulk_g2s(&s_rec[b][0], src + (size_t)3 * b * FWD_BATCH, (uint32_t)cnt * 48u, &s_bar[b]);
-        }
+        for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+        mbar_fence_init();
     }
+    if (VARIANT_B) s_touched[tid] = 0;   // FWD_BATCH == BLK
+    unsigned it = 0;   // batches issued to the mbarrier ring so far (identical in every thread)
 
-    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
-    unsigned last = 0;
-    bool done = !inside;
+    for (;;) {
+        if (tid == 0) s_unit = (int)atomicAdd(a.work, 1u);
+        __syncthreads();
+        const int unit = s_unit;
+        __syncthreads();
+        if (unit >= a.n_units) break;
+        const int tile = unit / UNITS_PER_TILE, half = unit % UNITS_PER_TILE;
+        const uint2 rg = a.ranges[tile];
+        const int n = (int)(rg.y - rg.x);
+        int px, py;
+        float rx0, ry0;
+        warp_region(tile, a.gx, half * WARPS + warp, lane, px, py, rx0, ry0);
+        const bool inside = px < a.W && py < a.H;
+        const float pxf = (float)px, pyf = (float)py;
+        const float4* src = a.records + (size_t)3 * rg.x;
+        const int nb = (n + FWD_BATCH - 1) / FWD_BATCH;
 
-    for (int b = 0; b < nb; b++) {
-        const int base = b * FWD_BATCH;
-        const int cnt = min(FWD_BATCH, n - base);
-        int stage;
-        if (TMA) {
-            stage = b % FWD_STAGES;
-            mbar_wait(&s_bar[stage], (uint32_t)((b / FWD_STAGES) & 1));
-            __syncwarp();   // the try_wait loop exits per thread: reconverge before the warp-wide code
-        } else {
-            stage = 0;
-            for (int k = tid; k < cnt * 3; k += BLK) s_rec[0][k] = src[(size_t)3 * base + k];
-            __syncthreads();
-        }
-        const float4* rec = s_rec[stage];
-        if (!__all_sync(FULL, done)) {
-            // pass 1: one splat per lane -> bitmask of the splats that can touch this warp's 8x4 block
-            unsigned mask[FWD_ROUNDS];
-#pragma unroll
-            for (int r = 0; r < FWD_ROUNDS; r++) {
-                const int jj = r * 32 + lane;
-                bool keep = false;
-                if (jj < cnt) keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
-                mask[r] = __ballot_sync(FULL, keep);
+        if (TMA && tid == 0) {
+            for (int b = 0; b < FWD_STAGES && b < nb; b++) {
+                const int cnt = min(FWD_BATCH, n - b * FWD_BATCH);
+                const int st = (int)((it + b) % FWD_STAGES);
+                mbar_expect_tx(&s_bar[st], (uint32_t)cnt * 48u);
+                tma_bulk_g2s(&s_rec[st][0], src + (size_t)3 * b * FWD_BATCH, (uint32_t)cnt * 48u, &s_bar[st]);
             }
-            // pass 2: front-to-back over the survivors (warp-uniform loop, per-lane predicates)
+        }
+
+        float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
+        unsigned last = 0;
+        bool done = !inside;
+        int issued = nb;
+
+        for (int b = 0; b < nb; b++) {
+            const int base = b * FWD_BATCH;
+            const int cnt = min(FWD_BATCH, n - base);
+            int stage;
+            if (TMA) {
+                stage = (int)((it + b) % FWD_STAGES);
+                mbar_wait(&s_bar[stage], (uint32_t)(((it + b) / FWD_STAGES) & 1));
+                __syncwarp();   // the try_wait loop exits per thread: reconverge before warp-wide code
+            } else {
+                stage = 0;
+                for (int k = tid; k < cnt * 3; k += BLK) s_rec[0][k] = src[(size_t)3 * base + k];
+                __syncthreads();
+            }
+            const float4* rec = s_rec[stage];
+            if (!__all_sync(FULL, done)) {
+                // pass 1: one splat per lane -> bitmask of the splats that can touch this warp's block
+                unsigned mask[FWD_ROUNDS];
 #pragma unroll
-            for (int r = 0; r < FWD_ROUNDS; r++) {
-                unsigned m = mask[r];
-                while (m) {
-                    const int j = r * 32 + __ffs(m) - 1;
-                    m &= m - 1;
-                    const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
-                    const float dx = r0.x - pxf, dy = r0.y - pyf;
-                    const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
-                    const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
-                    if (done || power2 > 0.f || alpha < 1.0f / 255.0f) continue;
-                    const float test_T = T * (1.f - alpha);
-                    if (test_T < 0.0001f) { done = true; continue; }
-                    const float4 r2 = rec[3 * j + 2];
-                    const float w = alpha * T;
-                    C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
-                    D += r0.w * w;
-                    A += w;
-                    if (VARIANT_B) {
-                        if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                for (int r = 0; r < FWD_ROUNDS; r++) {
+                    const int jj = r * 32 + lane;
+                    bool keep = false;
+                    if (jj < cnt) keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
+                    mask[r] = __ballot_sync(FULL, keep);
+                }
+                // pass 2: front-to-back over the survivors (warp-uniform loop, per-lane predicates)
+#pragma unroll
+                for (int r = 0; r < FWD_ROUNDS; r++) {
+                    unsigned m = mask[r];
+                    while (m) {
+                        const int j = r * 32 + __ffs(m) - 1;
+                        m &= m - 1;
+                        const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+                        const float dx = r0.x - pxf, dy = r0.y - pyf;
+                        const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
+                        const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
+                        if (done || power2 > 0.f || alpha < 1.0f / 255.0f) continue;
+                        const float test_T = T * (1.f - alpha);
+                        if (test_T < 0.0001f) { done = true; continue; }
+                        const float4 r2 = rec[3 * j + 2];
+                        const float w = alpha * T;
+                        C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
+                        D += r0.w * w;
+                        A += w;
+                        if (VARIANT_B) {
+                            if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                        }
+                        T = test_T;
+                        last = (unsigned)(base + j + 1);
                     }
-                    T = test_T;
-                    last = (unsigned)(base + j + 1);
                 }
             }
-        }
-        const int ndone = __syncthreads_count(done ? 1 : 0);
-        if (VARIANT_B && count_touched) {
-            if (tid < cnt) {
-                const int v = s_touched[tid];
-                if (v) {
-                    atomicAdd(&a.n_touched[__float_as_uint(rec[3 * tid].z)], v);
-                    s_touched[tid] = 0;
+            const int ndone = __syncthreads_count(done ? 1 : 0);
+            if (VARIANT_B && count_touched) {
+                if (tid < cnt) {
+                    const int v = s_touched[tid];
+                    if (v) {
+                        atomicAdd(&a.n_touched[__float_as_uint(rec[3 * tid].z)], v);
+                        s_touched[tid] = 0;
+                    }
                 }
+                __syncthreads();
             }
-            __syncthreads();
+            if (ndone == BLK) {
+                issued = min(nb, b + FWD_STAGES);
+                if (TMA)   // consume the copies still in flight: their stages are reused by the next unit
+                    for (int bb = b + 1; bb < issued; bb++)
+                        mbar_wait(&s_bar[(it + bb) % FWD_STAGES], (uint32_t)(((it + bb) / FWD_STAGES) & 1));
+                break;
+            }
+            if (TMA && tid == 0 && b + FWD_STAGES < nb) {
+                const int nbase = (b + FWD_STAGES) * FWD_BATCH;
+                const int ncnt = min(FWD_BATCH, n - nbase);
+                mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
+                tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
+            }
         }
-        if (ndone == BLK) {
-            if (TMA)   // drain copies still in flight before the CTA's shared memory is released
-                for (int bb = b + 1; bb < nb && bb < b + FWD_STAGES; bb++)
-                    mbar_wait(&s_bar[bb % FWD_STAGES], (uint32_t)((bb / FWD_STAGES) & 1));
-            break;
-        }
-        if (TMA && tid == 0 && b + FWD_STAGES < nb) {
-            const int nbase = (b + FWD_STAGES) * FWD_BATCH;
-            const int ncnt = min(FWD_BATCH, n - nbase);
-            mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
-            tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
-        }
-    }
-    __syncwarp();
+        it += (unsigned)issued;
+        __syncwarp();
 
-    if (inside) {
-        const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
-        a.final_T[pix] = T;
-        a.n_contrib[pix] = last;
-        a.out_color[pix] = C0 + T * __ldg(a.bg);
-        a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
-        a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
-        a.out_depth[pix] = D;
-        a.out_third[pix] = VARIANT_B ? 1.f - T : A;
+        if (inside) {
+            const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
+            a.final_T[pix] = T;
+            a.n_contrib[pix] = last;
+            a.out_color[pix] = C0 + T * __ldg(a.bg);
+            a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
+            a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
+            a.out_depth[pix] = D;
+            a.out_third[pix] = VARIANT_B ? 1.f - T : A;
+        }
+        const unsigned m = __reduce_max_sync(FULL, last);
+        if (lane == 0 && m) atomicMax(&a.tile_max[tile], m);   // tile_scan zeroed it
     }
-    const unsigned m = __reduce_max_sync(FULL, last);
-    if (lane == 0 && m) atomicMax(&s_max, m);
-    __syncthreads();
-    if (tid == 0) a.tile_max[tile] = s_max;
 }
 
 // ================================================================================================
@@ -271,7 +290,8 @@ constexpr int BWD_ROUNDS = BWD_BATCH / 32;
 constexpr int PART_STRIDE = 11;  // 10 components + 1 pad: conflict-free column reads in the flush
 
 struct BwdArgs {
-    int W, H, gx;
+    int W, H, gx, n_units;
+    unsigned* work;
     const uint2* ranges;
     const float4* records;
     const uint32_t* tile_max;
@@ -327,172 +347,201 @@ __global__ void __launch_bounds__(BLK)
 blend_bwd_kernel(BwdArgs a) {
     __shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[BWD_STAGES];
-    __shared__ float s_part[BLK / 32][BWD_BATCH][PART_STRIDE];
-    __shared__ unsigned long long s_mask[BLK / 32];
+    __shared__ float s_part[WARPS][BWD_BATCH][PART_STRIDE];
+    __shared__ unsigned long long s_mask[WARPS];
+    __shared__ int s_unit;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
-    const uint2 rg = a.ranges[tile];
-    const int n = min((int)(rg.y - rg.x), (int)a.tile_max[tile]);   // nothing past max n_contrib matters
-    if (n <= 0) return;
-    int px, py;
-    float rx0, ry0;
-    warp_region(tile, a.gx, warp, lane, px, py, rx0, ry0);
-    const bool inside = px < a.W && py < a.H;
-    const float pxf = (float)px, pyf = (float)py;
-    const float4* src = a.records + (size_t)3 * rg.x;
-    const int nb = (n + BWD_BATCH - 1) / BWD_BATCH;
+    if (TMA && tid == 0) {
+        for (int s = 0; s < BWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+        mbar_fence_init();
+    }
+    unsigned it = 0;
+    const float ddelx_dx = 0.5f * (float)a.W, ddely_dy = 0.5f * (float)a.H;
 
-    if (TMA) {
-        if (tid == 0) {
-            for (int s = 0; s < BWD_STAGES; s++) mbar_init(&s_bar[s], 1);
-            mbar_fence_init();
-        }
+    for (;;) {
+        if (tid == 0) s_unit = (int)atomicAdd(a.work, 1u);
         __syncthreads();
-        if (tid == 0) {
+        const int unit = s_unit;
+        __syncthreads();
+        if (unit >= a.n_units) break;
+        const int tile = unit / UNITS_PER_TILE, half = unit % UNITS_PER_TILE;
+        const uint2 rg = a.ranges[tile];
+        const int n = min((int)(rg.y - rg.x), (int)a.tile_max[tile]);   // nothing past max n_contrib matters
+        if (n <= 0) continue;
+        int px, py;
+        float rx0, ry0;
+        warp_region(tile, a.gx, half * WARPS + warp, lane, px, py, rx0, ry0);
+        const bool inside = px < a.W && py < a.H;
+        const float pxf = (float)px, pyf = (float)py;
+        const float4* src = a.records + (size_t)3 * rg.x;
+        const int nb = (n + BWD_BATCH - 1) / BWD_BATCH;
+
+        if (TMA && tid == 0) {
             for (int bi = 0; bi < BWD_STAGES && bi < nb; bi++) {
                 const int base = (nb - 1 - bi) * BWD_BATCH;
                 const int cnt = min(BWD_BATCH, n - base);
-                mbar_expect_tx(&s_bar[bi], (uint32_t)cnt * 48u);
-                tma_bulk_g2s(&s_rec[bi][0], src + (size_t)3 * base, (uint32_t)cnt * 48u, &s_bar[bi]);
+                const int st = (int)((it + bi) % BWD_STAGES);
+                mbar_expect_tx(&s_bar[st], (uint32_t)cnt * 48u);
+                tma_bulk_g2s(&s_rec[st][0], src + (size_t)3 * base, (uint32_t)cnt * 48u, &s_bar[st]);
             }
         }
-    }
 
-    // per-pixel state
-    float T_final = 1.f, dC0 = 0.f, dC1 = 0.f, dC2 = 0.f, dD = 0.f, dA = 0.f;
-    int last_contributor = 0;
-    if (inside) {
-        const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
-        T_final = a.final_T[pix];
-        last_contributor = (int)a.n_contrib[pix];
-        dC0 = a.dL_dcolor[pix]; dC1 = a.dL_dcolor[HW + pix]; dC2 = a.dL_dcolor[2 * HW + pix];
-        dD = a.dL_ddepth[pix];
-        dA = a.dL_dthird ? a.dL_dthird[pix] : 0.f;
-    }
-    const int warp_last = __reduce_max_sync(FULL, last_contributor);
-    float T = T_final;
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc_d = 0.f, acc_a = 0.f;
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
-    const float bg_dot = __ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2;
-    const float ddelx_dx = 0.5f * (float)a.W, ddely_dy = 0.5f * (float)a.H;
-
-    for (int bi = 0; bi < nb; bi++) {
-        const int base = (nb - 1 - bi) * BWD_BATCH;
-        const int cnt = min(BWD_BATCH, n - base);
-        int stage;
-        if (TMA) {
-            stage = bi % BWD_STAGES;
-            mbar_wait(&s_bar[stage], (uint32_t)((bi / BWD_STAGES) & 1));
-            __syncwarp();
-        } else {
-            stage = 0;
-            if (tid < cnt * 3) s_rec[0][tid] = src[(size_t)3 * base + tid];
-            __syncthreads();
+        // per-pixel state
+        float T_final = 1.f, dC0 = 0.f, dC1 = 0.f, dC2 = 0.f, dD = 0.f, dA = 0.f;
+        int last_contributor = 0;
+        if (inside) {
+            const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
+            T_final = a.final_T[pix];
+            last_contributor = (int)a.n_contrib[pix];
+            dC0 = a.dL_dcolor[pix]; dC1 = a.dL_dcolor[HW + pix]; dC2 = a.dL_dcolor[2 * HW + pix];
+            dD = a.dL_ddepth[pix];
+            dA = a.dL_dthird ? a.dL_dthird[pix] : 0.f;
         }
-        const float4* rec = s_rec[stage];
-        unsigned long long wrote = 0ull;
-        if (base < warp_last) {
-            // pass 1: cull against this warp's 8x4 block and its deepest contributor
-            unsigned mask[BWD_ROUNDS];
-#pragma unroll
-            for (int r = 0; r < BWD_ROUNDS; r++) {
-                const int jj = r * 32 + lane;
-                bool keep = false;
-                if (jj < cnt && base + jj < warp_last)
-                    keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
-                mask[r] = __ballot_sync(FULL, keep);
+        const int warp_last = __reduce_max_sync(FULL, last_contributor);
+        float T = T_final;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc_d = 0.f, acc_a = 0.f;
+        float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
+        const float tfb = -T_final * (__ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2);
+
+        for (int bi = 0; bi < nb; bi++) {
+            const int base = (nb - 1 - bi) * BWD_BATCH;
+            const int cnt = min(BWD_BATCH, n - base);
+            int stage;
+            if (TMA) {
+                stage = (int)((it + bi) % BWD_STAGES);
+                mbar_wait(&s_bar[stage], (uint32_t)(((it + bi) / BWD_STAGES) & 1));
+                __syncwarp();
+            } else {
+                stage = 0;
+                for (int k = tid; k < cnt * 3; k += BLK) s_rec[0][k] = src[(size_t)3 * base + k];
+                __syncthreads();
             }
-            // pass 2: back-to-front over the survivors
+            const float4* rec = s_rec[stage];
+            unsigned long long wrote = 0ull;
+            if (base < warp_last) {
+                // pass 1: cull against this warp's 8x4 block and its deepest contributor
+                unsigned mask[BWD_ROUNDS];
 #pragma unroll
-            for (int r = BWD_ROUNDS - 1; r >= 0; r--) {
-                unsigned m = mask[r];
-                while (m) {
-                    const int bit = 31 - __clz(m);
-                    m &= ~(1u << bit);
-                    const int j = r * 32 + bit;
-                    const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
-                    const float dx = r0.x - pxf, dy = r0.y - pyf;
-                    const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
-                    const float G = fast_exp2(power2);
-                    const float alpha = fminf(0.99f, r1.w * G);
-                    const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
-                                        (alpha >= 1.0f / 255.0f);
-                    if (!__any_sync(FULL, active)) continue;   // warp-uniform
-                    float v[10];
+                for (int r = 0; r < BWD_ROUNDS; r++) {
+                    const int jj = r * 32 + lane;
+                    bool keep = false;
+                    if (jj < cnt && base + jj < warp_last)
+                        keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
+                    mask[r] = __ballot_sync(FULL, keep);
+                }
+                // pass 2: back-to-front over the survivors
 #pragma unroll
-                    for (int k = 0; k < 10; k++) v[k] = 0.f;
-                    if (active) {
-                        const float4 r2 = rec[3 * j + 2];
-                        const float inv1ma = __fdividef(1.f, 1.f - alpha);
-                        T = T * inv1ma;
-                        const float w = alpha * T;
-                        float dL_dalpha;
-                        acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = r2.x;
-                        acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = r2.y;
-                        acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = r2.z;
-                        dL_dalpha = (r2.x - acc0) * dC0 + (r2.y - acc1) * dC1 + (r2.z - acc2) * dC2;
-                        v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2;
-                        acc_d = last_alpha * last_depth + (1.f - last_alpha) * acc_d; last_depth = r0.w;
-                        dL_dalpha += (r0.w - acc_d) * dD;
-                        v[9] = w * dD;
-                        acc_a = last_alpha + (1.f - last_alpha) * acc_a;
-                        dL_dalpha += (1.f - acc_a) * dA;
-                        dL_dalpha *= T;
-                        last_alpha = alpha;
-                        dL_dalpha += (-T_final * inv1ma) * bg_dot;
-                        const float dL_dG = r1.w * dL_dalpha;   // Q1: the 0.99 clamp is straight-through
-                        const float gdx = G * dx, gdy = G * dy;
-                        // true conic from the log2-scaled record: xx = -2 ln2 A, xy = -ln2 B, yy = -2 ln2 C
-                        const float cxx = -2.f * LN2 * r1.x, cxy = -LN2 * r1.y, cyy = -2.f * LN2 * r1.z;
-                        const float dG_ddelx = -gdx * cxx - gdy * cxy;
-                        const float dG_ddely = -gdy * cyy - gdx * cxy;
-                        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[1] = dL_dG * dG_ddely * ddely_dy;
-                        v[2] = -0.5f * gdx * dx * dL_dG;
-                        v[3] = -0.5f * gdx * dy * dL_dG;   // Q8: half the true off-diagonal derivative
-                        v[4] = -0.5f * gdy * dy * dL_dG;
-                        v[5] = G * dL_dalpha;
+                for (int r = BWD_ROUNDS - 1; r >= 0; r--) {
+                    unsigned m = mask[r];
+                    while (m) {
+                        const int bit = 31 - __clz(m);
+                        m &= ~(1u << bit);
+                        const int j = r * 32 + bit;
+                        const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
+                        const float dx = r0.x - pxf, dy = r0.y - pyf;
+                        const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
+                        const float G = fast_exp2(power2);
+                        const float alpha = fminf(0.99f, r1.w * G);
+                        const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
+                                            (alpha >= 1.0f / 255.0f);
+                        const unsigned act = __ballot_sync(FULL, active);
+                        if (!act) continue;   // warp-uniform
+                        // Per lane only the *moments* of gG = dL/dG * G are formed; the per-splat
+                        // constant factors (conic, 1/opacity, pixel scale) are applied once per
+                        // (unit, splat) in the flush below instead of once per pixel.
+                        float v[10];
+#pragma unroll
+                        for (int k = 0; k < 10; k++) v[k] = 0.f;
+                        if (active) {
+                            const float4 r2 = rec[3 * j + 2];
+                            const float inv1ma = fast_rcp(1.f - alpha);
+                            T = T * inv1ma;
+                            const float w = alpha * T;
+                            acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = r2.x;
+                            acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = r2.y;
+                            acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = r2.z;
+                            acc_d = fmaf(last_alpha, last_depth - acc_d, acc_d); last_depth = r0.w;
+                            acc_a = fmaf(last_alpha, 1.f - acc_a, acc_a);
+                            float d = (r2.x - acc0) * dC0;
+                            d = fmaf(r2.y - acc1, dC1, d);
+                            d = fmaf(r2.z - acc2, dC2, d);
+                            d = fmaf(r0.w - acc_d, dD, d);
+                            d = fmaf(1.f - acc_a, dA, d);
+                            d = fmaf(tfb, inv1ma, d * T);      // + (-T_final / (1 - alpha)) * (bg . dL/dC)
+                            last_alpha = alpha;
+                            const float gG = (r1.w * d) * G;   // Q1: the 0.99 clamp is straight-through
+                            const float m1 = gG * dx, m2 = gG * dy;
+                            v[0] = gG; v[1] = m1; v[2] = m2;
+                            v[3] = m1 * dx; v[4] = m1 * dy; v[5] = m2 * dy;
+                            v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2; v[9] = w * dD;
+                        }
+                        if ((act & (act - 1)) == 0) {
+                            // a single touched pixel: no reduction needed, the lane stores its row
+                            if (active) {
+#pragma unroll
+                                for (int k = 0; k < 10; k++) s_part[warp][j][k] = v[k];
+                            }
+                        } else {
+                            int slot;
+                            bool valid;
+                            const float tot = butterfly10(v, lane, slot, valid);
+                            if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
+                        }
+                        wrote |= 1ull << j;
                     }
-                    int slot;
-                    bool valid;
-                    const float tot = butterfly10(v, lane, slot, valid);
-                    if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
-                    wrote |= 1ull << j;
                 }
             }
-        }
-        if (lane == 0) s_mask[warp] = wrote;
-        __syncthreads();
-        if (tid < cnt) {
-            float g[12];
+            if (lane == 0) s_mask[warp] = wrote;
+            __syncthreads();
+            if (tid < cnt) {
+                float g[10];
 #pragma unroll
-            for (int k = 0; k < 12; k++) g[k] = 0.f;
-            bool any = false;
+                for (int k = 0; k < 10; k++) g[k] = 0.f;
+                bool any = false;
 #pragma unroll
-            for (int w = 0; w < BLK / 32; w++) {
-                if ((s_mask[w] >> tid) & 1ull) {
-                    any = true;
+                for (int w = 0; w < WARPS; w++) {
+                    if ((s_mask[w] >> tid) & 1ull) {
+                        any = true;
 #pragma unroll
-                    for (int k = 0; k < 10; k++) g[k] += s_part[w][tid][k];
+                        for (int k = 0; k < 10; k++) g[k] += s_part[w][tid][k];
+                    }
+                }
+                if (any) {
+                    const float4 q0 = rec[3 * tid], q1 = rec[3 * tid + 1];
+                    const unsigned idx = __float_as_uint(q0.z);
+                    // moments -> gradients: true conic from the log2-scaled record
+                    const float cxx = -2.f * LN2 * q1.x, cxy = -LN2 * q1.y, cyy = -2.f * LN2 * q1.z;
+                    const float dmx = -ddelx_dx * (cxx * g[1] + cxy * g[2]);
+                    const float dmy = -ddely_dy * (cyy * g[2] + cxy * g[1]);
+                    float4* dst = a.grad_acc + (size_t)3 * idx;
+                    // {dmean2D.x, dmean2D.y, dconic.xx, dconic.xy (half, Q8)} {dconic.yy, dopacity, dr, dg} {db, ddepth}
+                    atomicAdd(dst + 0, make_float4(dmx, dmy, -0.5f * g[3], -0.5f * g[4]));
+                    atomicAdd(dst + 1, make_float4(-0.5f * g[5], __fdividef(g[0], q1.w), g[6], g[7]));
+                    atomicAdd(reinterpret_cast<float2*>(dst + 2), make_float2(g[8], g[9]));
                 }
             }
-            if (any) {
-                const unsigned idx = __float_as_uint(rec[3 * tid].z);
-                float4* dst = a.grad_acc + (size_t)3 * idx;
-                atomicAdd(dst + 0, make_float4(g[0], g[1], g[2], g[3]));
-                atomicAdd(dst + 1, make_float4(g[4], g[5], g[6], g[7]));
-                atomicAdd(reinterpret_cast<float2*>(dst + 2), make_float2(g[8], g[9]));
+            __syncthreads();
+            if (TMA && tid == 0 && bi + BWD_STAGES < nb) {
+                const int nbase = (nb - 1 - (bi + BWD_STAGES)) * BWD_BATCH;
+                const int ncnt = min(BWD_BATCH, n - nbase);
+                mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
+                tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
             }
         }
-        __syncthreads();
-        if (TMA && tid == 0 && bi + BWD_STAGES < nb) {
-            const int nbase = (nb - 1 - (bi + BWD_STAGES)) * BWD_BATCH;
-            const int ncnt = min(BWD_BATCH, n - nbase);
-            mbar_expect_tx(&s_bar[stage], (uint32_t)ncnt * 48u);
-            tma_bulk_g2s(&s_rec[stage][0], src + (size_t)3 * nbase, (uint32_t)ncnt * 48u, &s_bar[stage]);
-        }
+        it += (unsigned)nb;
     }
+}
+
+// resident CTAs of a persistent kernel on the current device (occupancy x SM count), cached
+template <typename K>
+int persistent_grid(K kernel, int units) {
+    int dev = 0, sms = 148, occ = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, BLK, 0) != cudaSuccess || occ < 1) occ = 1;
+    const int slots = occ * sms;
+    return units < slots ? (units < 1 ? 1 : units) : slots;
 }
 
 }  // namespace
@@ -500,30 +549,32 @@ blend_bwd_kernel(BwdArgs a) {
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
                      int use_tma, cudaStream_t s) {
     FwdArgs a;
-    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx;
-    a.ctrl = img.ctrl; a.capacity = bin.capacity; a.ranges = img.ranges; a.records = bin.records;
+    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx; a.n_units = img.G * UNITS_PER_TILE;
+    a.ctrl = img.ctrl; a.work = &img.ctrl->work_fwd;
+    a.capacity = bin.capacity; a.ranges = img.ranges; a.records = bin.records;
     a.bg = v.bg; a.out_color = out.color; a.out_depth = out.depth; a.out_third = out.third;
     a.n_touched = out.n_touched; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.tile_max = img.tile_max;
     if (v.variant == EAGS_VARIANT_B) {
-        if (use_tma) blend_fwd_kernel<true, true><<<img.G, BLK, 0, s>>>(a);
-        else blend_fwd_kernel<true, false><<<img.G, BLK, 0, s>>>(a);
+        if (use_tma) blend_fwd_kernel<true, true><<<persistent_grid(blend_fwd_kernel<true, true>, a.n_units), BLK, 0, s>>>(a);
+        else blend_fwd_kernel<true, false><<<persistent_grid(blend_fwd_kernel<true, false>, a.n_units), BLK, 0, s>>>(a);
     } else {
-        if (use_tma) blend_fwd_kernel<false, true><<<img.G, BLK, 0, s>>>(a);
-        else blend_fwd_kernel<false, false><<<img.G, BLK, 0, s>>>(a);
+        if (use_tma) blend_fwd_kernel<false, true><<<persistent_grid(blend_fwd_kernel<false, true>, a.n_units), BLK, 0, s>>>(a);
+        else blend_fwd_kernel<false, false><<<persistent_grid(blend_fwd_kernel<false, false>, a.n_units), BLK, 0, s>>>(a);
     }
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
 int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
-                     float* grad_acc, int use_tma, cudaStream_t s) {
+                     float* grad_acc, unsigned* work, int use_tma, cudaStream_t s) {
     BwdArgs a;
-    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx;
+    a.W = v.image_width; a.H = v.image_height; a.gx = img.gx; a.n_units = img.G * UNITS_PER_TILE;
+    a.work = work;
     a.ranges = img.ranges; a.records = bin.records; a.tile_max = img.tile_max;
     a.final_T = img.final_T; a.n_contrib = img.n_contrib; a.bg = v.bg;
     a.dL_dcolor = gin.dL_dcolor; a.dL_ddepth = gin.dL_ddepth; a.dL_dthird = gin.dL_dthird;
     a.grad_acc = (float4*)grad_acc;
-    if (use_tma) blend_bwd_kernel<true><<<img.G, BLK, 0, s>>>(a);
-    else blend_bwd_kernel<false><<<img.G, BLK, 0, s>>>(a);
+    if (use_tma) blend_bwd_kernel<true><<<persistent_grid(blend_bwd_kernel<true>, a.n_units), BLK, 0, s>>>(a);
+    else blend_bwd_kernel<false><<<persistent_grid(blend_bwd_kernel<false>, a.n_units), BLK, 0, s>>>(a);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }

@@ -140,7 +140,7 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
     float* grad_acc = (float*)((char*)scratch + SL.grad_acc);
     double* pose_acc = (double*)((char*)scratch + SL.pose);
     CHECK_CUDA(cudaMemsetAsync(scratch, 0, SL.pose + 256, s), "memset(scratch)");
-    CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, g_opt_tma.load(), s), "blend_bwd");
+    CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, (unsigned*)((char*)scratch + SL.pose + 128), g_opt_tma.load(), s), "blend_bwd");
     CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, s), "preprocess_bwd");
     return 0;
 }

@@ -79,7 +79,7 @@ int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, cudaStream_t
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
                      int use_tma, cudaStream_t s);
 int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
-                     float* grad_acc, int use_tma, cudaStream_t s);
+                     float* grad_acc, unsigned* work, int use_tma, cudaStream_t s);
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
                           GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
                           double* pose_acc, cudaStream_t s);

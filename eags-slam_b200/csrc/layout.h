@@ -41,7 +41,9 @@ struct EagsCtrl {
     unsigned long long num_rendered;   // K = sum tiles_touched (atomics in preprocess_fwd)
     unsigned long long num_scanned;    // K as seen by tile_scan (debug cross-check)
     unsigned int n_big;                // entries in big_list
-    unsigned int pad[11];
+    unsigned int work_sort;            // dynamic work queues of the persistent kernels
+    unsigned int work_fwd;
+    unsigned int pad[9];
 };
 static_assert(sizeof(EagsCtrl) == 64, "ctrl block is 64 bytes");
 
@@ -100,7 +102,7 @@ static inline BinningLayout binning_layout(int64_t cap, int with_keys) {
     return L;
 }
 
-// backward scratch: grad_acc float[P][12] | pose accumulators double[16]
+// backward scratch: grad_acc float[P][12] | pose accumulators double[16] | work queue u32 (at pose + 128)
 struct ScratchLayout {
     size_t grad_acc, pose, total;
 };
