@@ -1,0 +1,152 @@
+"""Keyframe-batch mapping over several GPUs, and submap placement for parallel loop closure.
+
+The reference optimises a submap on one GPU, one random keyframe view per iteration
+(src/entities/mapper.py:143-170), and runs loop-closure registration in one worker thread on one
+other device (src/entities/lc.py:60,625).  It has no collective anywhere.
+This module is the multi-GPU extension of SURVEY 8(e):
+
+* **sharded mapping** -- the path shards over *views*.  One process per GPU; every rank holds a
+  full replica of the submap's parameters and optimiser state, renders its own keyframe view(s) of the
+  step, and the parameter gradients are summed with ONE all-reduce over a fused flat buffer
+  (:class:`FusedGradBucket`: ``p.grad`` of every parameter is a view into it, so autograd
+  accumulates in place and nothing is packed or unpacked), divided by the number of views, and the
+  identical optimiser step is taken on every rank.  At world_size 1 with one view per step this is
+  exactly the reference's step.
+* **parallel loop closure** -- independent submaps are placed round-robin, no collective
+  (:func:`assign_submaps`).
+
+Only ``torch.distributed`` is used for the plumbing (NCCL on the GPUs; the host logic is tested with
+gloo on CPU, tests/test_sharded_gloo.py).  Nothing here touches the rasterizer kernels; the render
+function is whatever the caller passes (``render_gaussian_model`` of the reference, utils.py:120).
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def _world() -> int:
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def _rank() -> int:
+    return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+
+
+def shard_views(n_views: int, rank: Optional[int] = None, world: Optional[int] = None) -> List[int]:
+    """Indices of the views of one step that ``rank`` renders (round-robin: view v -> rank v % world)."""
+    rank = _rank() if rank is None else rank
+    world = _world() if world is None else world
+    return [v for v in range(int(n_views)) if v % world == rank]
+
+
+def assign_submaps(n_submaps: int, rank: Optional[int] = None, world: Optional[int] = None) -> List[int]:
+    """Independent submap jobs of parallel loop closure handled by ``rank`` (no collective)."""
+    return shard_views(n_submaps, rank, world)
+
+
+class FusedGradBucket:
+    """One flat fp32 buffer holding the gradients of all parameters, in the given order.
+
+    ``attach()`` zeroes the buffer (one memset) and points every ``p.grad`` at its slice, so
+    ``backward()`` accumulates straight into the bucket; ``all_reduce()`` is then a single
+    collective over ``11 * P`` floats for a submap (xyz 3 + scale 3 + rotation 4 + opacity 1).
+    """
+
+    def __init__(self, params: Sequence[torch.Tensor]):
+        self.params = list(params)
+        if not self.params:
+            raise ValueError("FusedGradBucket needs at least one parameter")
+        dev, dt = self.params[0].device, self.params[0].dtype
+        for p in self.params:
+            if p.device != dev or p.dtype != dt:
+                raise ValueError("all parameters of a bucket must share device and dtype")
+        self.numel = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(self.numel, dtype=dt, device=dev)
+        self.views, off = [], 0
+        for p in self.params:
+            self.views.append(self.flat[off:off + p.numel()].view(p.shape))
+            off += p.numel()
+
+    def matches(self, params: Sequence[torch.Tensor]) -> bool:
+        params = list(params)
+        return len(params) == len(self.params) and all(
+            a is b and a.shape == v.shape for a, b, v in zip(params, self.params, self.views))
+
+    def attach(self) -> None:
+        self.flat.zero_()
+        for p, v in zip(self.params, self.views):
+            p.grad = v
+
+    def all_reduce(self, divide_by: float = 1.0, async_op: bool = False):
+        work = None
+        if _world() > 1:
+            work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
+        if divide_by != 1.0:
+            if work is not None and async_op:
+                work.wait()
+                work = None
+            self.flat.mul_(1.0 / float(divide_by))
+        return work
+
+
+def broadcast_parameters(params: Iterable[torch.Tensor], src: int = 0) -> None:
+    """Make every replica start from rank ``src``'s values."""
+    if _world() == 1:
+        return
+    with torch.no_grad():
+        for p in params:
+            dist.broadcast(p.data, src=src)
+
+
+def consistent_mask(mask: torch.Tensor) -> torch.Tensor:
+    """Prune/keep decisions must be identical on all ranks so P stays the same everywhere
+    (reference prunes inside the optimisation loop, mapper.py:201-223): a Gaussian is removed only
+    if every rank agrees (logical AND via MIN all-reduce)."""
+    if _world() == 1:
+        return mask
+    m = mask.to(torch.int32)
+    dist.all_reduce(m, op=dist.ReduceOp.MIN)
+    return m.to(torch.bool)
+
+
+class ShardedMapper:
+    """Data-parallel submap optimisation over keyframe views.
+
+    ``loss_fn(view) -> scalar tensor`` renders one view with the *local* replica and returns its
+    loss (e.g. the body of the reference's ``optimize_submap`` iteration, mapper.py:152-167).
+    ``reg_fn() -> scalar`` is an optional view-independent regulariser (isotropic loss,
+    mapper.py:166) added once, on every rank identically, after the all-reduce division.
+    """
+
+    def __init__(self, params: Sequence[torch.Tensor], optimizer: torch.optim.Optimizer,
+                 broadcast: bool = True):
+        self.optimizer = optimizer
+        self.bucket = FusedGradBucket(params)
+        if broadcast:
+            broadcast_parameters(self.bucket.params)
+
+    def rebuild(self, params: Sequence[torch.Tensor], optimizer: Optional[torch.optim.Optimizer] = None) -> None:
+        """After add/prune changed P (gaussian_model.py:519-583) the bucket is re-carved."""
+        self.bucket = FusedGradBucket(params)
+        if optimizer is not None:
+            self.optimizer = optimizer
+
+    def step(self, views: Sequence, loss_fn: Callable, reg_fn: Optional[Callable] = None) -> Dict:
+        """One optimisation step over ``views`` (all ranks pass the same list).  Returns the local
+        loss sum as a *tensor* (no host sync) and the number of views rendered locally."""
+        world, rank = _world(), _rank()
+        mine = [views[i] for i in shard_views(len(views), rank, world)]
+        self.bucket.attach()
+        local = None
+        for v in mine:
+            loss = loss_fn(v)
+            loss.backward()
+            local = loss.detach() if local is None else local + loss.detach()
+        self.bucket.all_reduce(divide_by=float(len(views)))
+        if reg_fn is not None:
+            reg_fn().backward()      # accumulates into the (already averaged) bucket, same on all ranks
+        self.optimizer.step()
+        return {"local_loss_sum": local, "local_views": len(mine)}
