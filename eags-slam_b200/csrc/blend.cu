@@ -12,10 +12,11 @@
 // id -> xy / conic / colour / depth from four arrays behind a __syncthreads per batch.
 //
 // blend_bwd replaces upstream's 10 global atomics per (pixel, Gaussian) pair by
-//   (1) a 12-shuffle transposing butterfly that reduces the 10 gradient components over the 32
-//       pixels of a warp (skipped altogether when no lane of the warp is touched by the Gaussian),
-//   (2) per-warp partial slabs in shared memory summed in fixed order once per batch, and
-//   (3) three 16-byte vector atomics per (tile, Gaussian) into a 48-byte accumulator row.
+//   (1) a pixel-per-lane pass that forms only two scalars per pair (gG = dL/dG * G and w = alpha * T;
+//       dL/dalpha in suffix-sum form needs one running scalar instead of five accumulators),
+//   (2) a transposed, splat-per-lane pass that sums the ten gradient moments of a splat over the
+//       warp's 32 pixels in registers (flush_slots), and
+//   (3) three vector atomics per (8x4 block, Gaussian) into a 48-byte accumulator row.
 // The walk starts at the tile's max n_contrib instead of the end of the list.
 //
 // Tensor cores are not used: blending is a per-pixel ordered recurrence, not a contraction; the
@@ -287,7 +288,8 @@ blend_fwd_kernel(FwdArgs a) {
 constexpr int BWD_BATCH = 64;    // records per stage (3 KB); also the width of the per-warp bitmask
 constexpr int BWD_STAGES = 3;
 constexpr int BWD_ROUNDS = BWD_BATCH / 32;
-constexpr int PART_STRIDE = 11;  // 10 components + 1 pad: conflict-free column reads in the flush
+constexpr int SLOTS = 16;        // (warp, splat) survivors buffered before a transposed accumulation
+constexpr int SLOT_STRIDE = 33;  // float2 row stride: conflict-free row writes and column reads
 
 struct BwdArgs {
     int W, H, gx, n_units;
@@ -304,42 +306,62 @@ struct BwdArgs {
     float4* grad_acc;         // [P][3]
 };
 
-// Sum v[0..9] over the 32 lanes with 12 shuffles.  Each stage halves the number of values a lane
-// owns while doubling the number of lanes already folded in.  On return lanes with `valid` hold
-// the warp total of component `slot` (two lanes per component; bit 0 of the lane distinguishes).
-__device__ __forceinline__ float butterfly10(const float v[10], int lane, int& slot, bool& valid) {
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-    float r[5];
+// Transposed accumulation ("phase 2").  Phase 1 runs pixel-per-lane and leaves, for each of up to 16
+// buffered (warp, splat) survivors, the two per-pixel scalars gG = dL/dG * G and w = alpha * T in
+// shared memory.  Here the roles flip: lane (s, h) owns survivor s and sums its ten gradient moments
+// over the 16 pixels of block half h in registers -- no cross-lane reduction except one xor-16 fold --
+// then applies the per-splat constant factors (conic, 1/opacity, pixel scale) once and commits
+// with three vector atomics.  Replaces a 12-shuffle / 20-select butterfly per (warp, splat).
+__device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], const float4* pixg,
+                                            const float4* rec, int count, int myj, int lane, float rx0,
+                                            float ry0, float ddelx_dx, float ddely_dy, float4* grad_acc) {
+    __syncwarp();
+    const int s = lane & 15, h = lane >> 4;
+    float v[10];
 #pragma unroll
-    for (int k = 0; k < 5; k++) {
-        const float send = b4 ? v[k] : v[k + 5];
-        const float keep = b4 ? v[k + 5] : v[k];
-        r[k] = keep + __shfl_xor_sync(FULL, send, 16);
-    }
-    float q[3];
+    for (int k = 0; k < 10; k++) v[k] = 0.f;
+    const bool mine = s < count;
+    float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (mine) {
+        q0 = rec[3 * myj];
+        float dxc[8], dyr[2];
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        const float hi = (k + 3 < 5) ? r[k + 3] : 0.f;
-        const float send = b3 ? r[k] : hi;
-        const float keep = b3 ? hi : r[k];
-        q[k] = keep + __shfl_xor_sync(FULL, send, 8);
+        for (int c = 0; c < 8; c++) dxc[c] = q0.x - (rx0 + (float)c);
+#pragma unroll
+        for (int r = 0; r < 2; r++) dyr[r] = q0.y - (ry0 + (float)(2 * h + r));
+        const float2* row = gw[s] + 16 * h;
+        const float4* pg = pixg + 16 * h;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const float2 e = row[i];
+            const float4 pc = pg[i];
+            const float dx = dxc[i & 7], dy = dyr[i >> 3];
+            const float m1 = e.x * dx, m2 = e.x * dy;
+            v[0] += e.x; v[1] += m1; v[2] += m2;
+            v[3] = fmaf(m1, dx, v[3]); v[4] = fmaf(m1, dy, v[4]); v[5] = fmaf(m2, dy, v[5]);
+            v[6] = fmaf(e.y, pc.x, v[6]); v[7] = fmaf(e.y, pc.y, v[7]);
+            v[8] = fmaf(e.y, pc.z, v[8]); v[9] = fmaf(e.y, pc.w, v[9]);
+        }
     }
-    float p0, p1;
-    {
-        const float send0 = b2 ? q[0] : q[2];
-        const float keep0 = b2 ? q[2] : q[0];
-        p0 = keep0 + __shfl_xor_sync(FULL, send0, 4);
-        const float send1 = b2 ? q[1] : 0.f;
-        const float keep1 = b2 ? 0.f : q[1];
-        p1 = keep1 + __shfl_xor_sync(FULL, send1, 4);
+#pragma unroll
+    for (int k = 0; k < 10; k++) v[k] += __shfl_xor_sync(FULL, v[k], 16);
+    if (mine) {
+        const float4 q1 = rec[3 * myj + 1];
+        float4* dst = grad_acc + (size_t)3 * __float_as_uint(q0.z);
+        if (h == 0) {
+            // moments -> gradients: true conic from the log2-scaled record
+            const float cxx = -2.f * LN2 * q1.x, cxy = -LN2 * q1.y, cyy = -2.f * LN2 * q1.z;
+            const float dmx = -ddelx_dx * (cxx * v[1] + cxy * v[2]);
+            const float dmy = -ddely_dy * (cyy * v[2] + cxy * v[1]);
+            // {dmean2D.x, dmean2D.y, dconic.xx, dconic.xy (half, Q8)}
+            atomicAdd(dst + 0, make_float4(dmx, dmy, -0.5f * v[3], -0.5f * v[4]));
+        } else {
+            // {dconic.yy, dopacity, dr, dg} {db, ddepth}
+            atomicAdd(dst + 1, make_float4(-0.5f * v[5], __fdividef(v[0], q1.w), v[6], v[7]));
+            atomicAdd(reinterpret_cast<float2*>(dst + 2), make_float2(v[8], v[9]));
+        }
     }
-    const float send = b1 ? p0 : p1;
-    const float keep = b1 ? p1 : p0;
-    float o = keep + __shfl_xor_sync(FULL, send, 2);
-    o += __shfl_xor_sync(FULL, o, 1);
-    slot = (b4 ? 5 : 0) + (b3 ? 3 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
-    valid = !(b2 && b1) && !(b3 && b2);
-    return o;
+    __syncwarp();
 }
 
 template <bool TMA>
@@ -347,8 +369,8 @@ __global__ void __launch_bounds__(BLK)
 blend_bwd_kernel(BwdArgs a) {
     __shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[BWD_STAGES];
-    __shared__ float s_part[WARPS][BWD_BATCH][PART_STRIDE];
-    __shared__ unsigned long long s_mask[WARPS];
+    __shared__ __align__(16) float2 s_gw[WARPS][SLOTS][SLOT_STRIDE];
+    __shared__ __align__(16) float4 s_pix[WARPS][32];
     __shared__ int s_unit;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -398,11 +420,14 @@ blend_bwd_kernel(BwdArgs a) {
             dD = a.dL_ddepth[pix];
             dA = a.dL_dthird ? a.dL_dthird[pix] : 0.f;
         }
+        s_pix[warp][lane] = make_float4(dC0, dC1, dC2, dD);   // phase 2 reads it after a __syncwarp
         const int warp_last = __reduce_max_sync(FULL, last_contributor);
         float T = T_final;
-        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc_d = 0.f, acc_a = 0.f;
-        float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
-        const float tfb = -T_final * (__ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2);
+        // A.4 in suffix-sum form.  With e_j = rgb_j . dL/dC + z_j dL/dD + dL/dA and
+        // S_i = sum_{k > i} e_k w_k + T_final (bg . dL/dC):   dL/dalpha_i = e_i T_i - S_i / (1 - alpha_i)
+        // (identical to upstream's accum_rec recurrence; one scalar instead of five accumulators).
+        float S = T_final * (__ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2);
+        int nslot = 0, myj = 0;
 
         for (int bi = 0; bi < nb; bi++) {
             const int base = (nb - 1 - bi) * BWD_BATCH;
@@ -418,7 +443,6 @@ blend_bwd_kernel(BwdArgs a) {
                 __syncthreads();
             }
             const float4* rec = s_rec[stage];
-            unsigned long long wrote = 0ull;
             if (base < warp_last) {
                 // pass 1: cull against this warp's 8x4 block and its deepest contributor
                 unsigned mask[BWD_ROUNDS];
@@ -430,7 +454,7 @@ blend_bwd_kernel(BwdArgs a) {
                         keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
                     mask[r] = __ballot_sync(FULL, keep);
                 }
-                // pass 2: back-to-front over the survivors
+                // pass 2: back-to-front over the survivors, pixel per lane
 #pragma unroll
                 for (int r = BWD_ROUNDS - 1; r >= 0; r--) {
                     unsigned m = mask[r];
@@ -445,83 +469,37 @@ blend_bwd_kernel(BwdArgs a) {
                         const float alpha = fminf(0.99f, r1.w * G);
                         const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
                                             (alpha >= 1.0f / 255.0f);
-                        const unsigned act = __ballot_sync(FULL, active);
-                        if (!act) continue;   // warp-uniform
-                        // Per lane only the *moments* of gG = dL/dG * G are formed; the per-splat
-                        // constant factors (conic, 1/opacity, pixel scale) are applied once per
-                        // (unit, splat) in the flush below instead of once per pixel.
-                        float v[10];
-#pragma unroll
-                        for (int k = 0; k < 10; k++) v[k] = 0.f;
+                        if (!__any_sync(FULL, active)) continue;   // warp-uniform
+                        float gG = 0.f, w = 0.f;
                         if (active) {
                             const float4 r2 = rec[3 * j + 2];
                             const float inv1ma = fast_rcp(1.f - alpha);
-                            T = T * inv1ma;
-                            const float w = alpha * T;
-                            acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = r2.x;
-                            acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = r2.y;
-                            acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = r2.z;
-                            acc_d = fmaf(last_alpha, last_depth - acc_d, acc_d); last_depth = r0.w;
-                            acc_a = fmaf(last_alpha, 1.f - acc_a, acc_a);
-                            float d = (r2.x - acc0) * dC0;
-                            d = fmaf(r2.y - acc1, dC1, d);
-                            d = fmaf(r2.z - acc2, dC2, d);
-                            d = fmaf(r0.w - acc_d, dD, d);
-                            d = fmaf(1.f - acc_a, dA, d);
-                            d = fmaf(tfb, inv1ma, d * T);      // + (-T_final / (1 - alpha)) * (bg . dL/dC)
-                            last_alpha = alpha;
-                            const float gG = (r1.w * d) * G;   // Q1: the 0.99 clamp is straight-through
-                            const float m1 = gG * dx, m2 = gG * dy;
-                            v[0] = gG; v[1] = m1; v[2] = m2;
-                            v[3] = m1 * dx; v[4] = m1 * dy; v[5] = m2 * dy;
-                            v[6] = w * dC0; v[7] = w * dC1; v[8] = w * dC2; v[9] = w * dD;
+                            T = T * inv1ma;                      // transmittance in front of splat j
+                            w = alpha * T;
+                            float e = fmaf(r2.x, dC0, dA);
+                            e = fmaf(r2.y, dC1, e);
+                            e = fmaf(r2.z, dC2, e);
+                            e = fmaf(r0.w, dD, e);
+                            const float d = fmaf(e, T, -S * inv1ma);
+                            S = fmaf(e, w, S);
+                            gG = (r1.w * d) * G;                 // Q1: the 0.99 clamp is straight-through
                         }
-                        if ((act & (act - 1)) == 0) {
-                            // a single touched pixel: no reduction needed, the lane stores its row
-                            if (active) {
-#pragma unroll
-                                for (int k = 0; k < 10; k++) s_part[warp][j][k] = v[k];
-                            }
-                        } else {
-                            int slot;
-                            bool valid;
-                            const float tot = butterfly10(v, lane, slot, valid);
-                            if (valid && !(lane & 1)) s_part[warp][j][slot] = tot;
+                        s_gw[warp][nslot][lane] = make_float2(gG, w);
+                        if ((lane & 15) == nslot) myj = j;
+                        if (++nslot == SLOTS) {
+                            flush_slots(s_gw[warp], s_pix[warp], rec, SLOTS, myj, lane, rx0, ry0, ddelx_dx,
+                                        ddely_dy, a.grad_acc);
+                            nslot = 0;
                         }
-                        wrote |= 1ull << j;
                     }
                 }
-            }
-            if (lane == 0) s_mask[warp] = wrote;
-            __syncthreads();
-            if (tid < cnt) {
-                float g[10];
-#pragma unroll
-                for (int k = 0; k < 10; k++) g[k] = 0.f;
-                bool any = false;
-#pragma unroll
-                for (int w = 0; w < WARPS; w++) {
-                    if ((s_mask[w] >> tid) & 1ull) {
-                        any = true;
-#pragma unroll
-                        for (int k = 0; k < 10; k++) g[k] += s_part[w][tid][k];
-                    }
-                }
-                if (any) {
-                    const float4 q0 = rec[3 * tid], q1 = rec[3 * tid + 1];
-                    const unsigned idx = __float_as_uint(q0.z);
-                    // moments -> gradients: true conic from the log2-scaled record
-                    const float cxx = -2.f * LN2 * q1.x, cxy = -LN2 * q1.y, cyy = -2.f * LN2 * q1.z;
-                    const float dmx = -ddelx_dx * (cxx * g[1] + cxy * g[2]);
-                    const float dmy = -ddely_dy * (cyy * g[2] + cxy * g[1]);
-                    float4* dst = a.grad_acc + (size_t)3 * idx;
-                    // {dmean2D.x, dmean2D.y, dconic.xx, dconic.xy (half, Q8)} {dconic.yy, dopacity, dr, dg} {db, ddepth}
-                    atomicAdd(dst + 0, make_float4(dmx, dmy, -0.5f * g[3], -0.5f * g[4]));
-                    atomicAdd(dst + 1, make_float4(-0.5f * g[5], __fdividef(g[0], q1.w), g[6], g[7]));
-                    atomicAdd(reinterpret_cast<float2*>(dst + 2), make_float2(g[8], g[9]));
+                if (nslot) {   // the records leave shared memory with this batch
+                    flush_slots(s_gw[warp], s_pix[warp], rec, nslot, myj, lane, rx0, ry0, ddelx_dx, ddely_dy,
+                                a.grad_acc);
+                    nslot = 0;
                 }
             }
-            __syncthreads();
+            __syncthreads();   // every warp is done with this stage
             if (TMA && tid == 0 && bi + BWD_STAGES < nb) {
                 const int nbase = (nb - 1 - (bi + BWD_STAGES)) * BWD_BATCH;
                 const int ncnt = min(BWD_BATCH, n - nbase);
