@@ -313,7 +313,7 @@ struct BwdArgs {
 // then applies the per-splat constant factors (conic, 1/opacity, pixel scale) once and commits
 // with three vector atomics.  Replaces a 12-shuffle / 20-select butterfly per (warp, splat).
 __device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], const float4* pixg,
-                                            const float4* rec, int count, int myj, int lane, float rx0,
+                                            const float4* meta, int count, int lane, float rx0,
                                             float ry0, float ddelx_dx, float ddely_dy, float4* grad_acc) {
     __syncwarp();
     const int s = lane & 15, h = lane >> 4;
@@ -323,7 +323,7 @@ __device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], con
     const bool mine = s < count;
     float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f);
     if (mine) {
-        q0 = rec[3 * myj];
+        q0 = meta[2 * s];
         float dxc[8], dyr[2];
 #pragma unroll
         for (int c = 0; c < 8; c++) dxc[c] = q0.x - (rx0 + (float)c);
@@ -346,7 +346,7 @@ __device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], con
 #pragma unroll
     for (int k = 0; k < 10; k++) v[k] += __shfl_xor_sync(FULL, v[k], 16);
     if (mine) {
-        const float4 q1 = rec[3 * myj + 1];
+        const float4 q1 = meta[2 * s + 1];
         float4* dst = grad_acc + (size_t)3 * __float_as_uint(q0.z);
         if (h == 0) {
             // moments -> gradients: true conic from the log2-scaled record
@@ -371,6 +371,7 @@ blend_bwd_kernel(BwdArgs a) {
     __shared__ __align__(8) uint64_t s_bar[BWD_STAGES];
     __shared__ __align__(16) float2 s_gw[WARPS][SLOTS][SLOT_STRIDE];
     __shared__ __align__(16) float4 s_pix[WARPS][32];
+    __shared__ __align__(16) float4 s_meta[WARPS][SLOTS * 2];   // records R0, R1 of the buffered survivors
     __shared__ int s_unit;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -427,7 +428,7 @@ blend_bwd_kernel(BwdArgs a) {
         // S_i = sum_{k > i} e_k w_k + T_final (bg . dL/dC):   dL/dalpha_i = e_i T_i - S_i / (1 - alpha_i)
         // (identical to upstream's accum_rec recurrence; one scalar instead of five accumulators).
         float S = T_final * (__ldg(a.bg) * dC0 + __ldg(a.bg + 1) * dC1 + __ldg(a.bg + 2) * dC2);
-        int nslot = 0, myj = 0;
+        int nslot = 0;   // survivors are carried across batches and flushed 16 at a time
 
         for (int bi = 0; bi < nb; bi++) {
             const int base = (nb - 1 - bi) * BWD_BATCH;
@@ -485,18 +486,16 @@ blend_bwd_kernel(BwdArgs a) {
                             gG = (r1.w * d) * G;                 // Q1: the 0.99 clamp is straight-through
                         }
                         s_gw[warp][nslot][lane] = make_float2(gG, w);
-                        if ((lane & 15) == nslot) myj = j;
+                        if (lane == 0) {
+                            s_meta[warp][2 * nslot] = r0;
+                            s_meta[warp][2 * nslot + 1] = r1;
+                        }
                         if (++nslot == SLOTS) {
-                            flush_slots(s_gw[warp], s_pix[warp], rec, SLOTS, myj, lane, rx0, ry0, ddelx_dx,
+                            flush_slots(s_gw[warp], s_pix[warp], s_meta[warp], SLOTS, lane, rx0, ry0, ddelx_dx,
                                         ddely_dy, a.grad_acc);
                             nslot = 0;
                         }
                     }
-                }
-                if (nslot) {   // the records leave shared memory with this batch
-                    flush_slots(s_gw[warp], s_pix[warp], rec, nslot, myj, lane, rx0, ry0, ddelx_dx, ddely_dy,
-                                a.grad_acc);
-                    nslot = 0;
                 }
             }
             __syncthreads();   // every warp is done with this stage
@@ -508,6 +507,9 @@ blend_bwd_kernel(BwdArgs a) {
             }
         }
         it += (unsigned)nb;
+        if (nslot)
+            flush_slots(s_gw[warp], s_pix[warp], s_meta[warp], nslot, lane, rx0, ry0, ddelx_dx, ddely_dy,
+                        a.grad_acc);
     }
 }
 
