@@ -364,8 +364,11 @@ __device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], con
     __syncwarp();
 }
 
+#ifndef BWD_MIN_CTAS
+#define BWD_MIN_CTAS 7
+#endif
 template <bool TMA>
-__global__ void __launch_bounds__(BLK)
+__global__ void __launch_bounds__(BLK, BWD_MIN_CTAS)
 blend_bwd_kernel(BwdArgs a) {
     __shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[BWD_STAGES];

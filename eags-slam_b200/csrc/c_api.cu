@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 #include "kernels.h"
 
@@ -12,6 +13,27 @@ namespace {
 thread_local char g_err[512] = "";
 std::atomic<int> g_opt_tma{1};
 std::atomic<unsigned long long> g_launches{0};
+
+// Optional per-kernel timing ("kernel_timing" option): CUDA events recorded on the caller's stream
+// around every launcher, read back (and synchronised) by eags_kernel_times().  Off by default: the
+// product path never records events.
+std::atomic<int> g_opt_timing{0};
+struct TimedSpan { const char* name; cudaEvent_t beg, end; };
+thread_local std::vector<TimedSpan> g_spans;
+thread_local std::vector<cudaEvent_t> g_event_pool;
+cudaEvent_t take_event() {
+    if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+struct ScopedSpan {
+    cudaStream_t s; bool on; TimedSpan span;
+    ScopedSpan(const char* name, cudaStream_t st) : s(st), on(g_opt_timing.load() != 0) {
+        if (on) { span.name = name; span.beg = take_event(); span.end = take_event(); cudaEventRecord(span.beg, s); }
+    }
+    ~ScopedSpan() { if (on) { cudaEventRecord(span.end, s); g_spans.push_back(span); } }
+};
 
 int fail(int code, const char* what) {
     snprintf(g_err, sizeof(g_err), "%s", what);
@@ -25,7 +47,8 @@ int fail_cuda(const char* where) {
 }
 #define CHECK_LAUNCH(expr, where)                 \
     do {                                          \
-        int n__ = (expr);                         \
+        int n__;                                  \
+        { ScopedSpan span__(where, s); n__ = (expr); } \
         if (n__ < 0) return fail_cuda(where);     \
         g_launches.fetch_add((unsigned)n__);      \
     } while (0)
@@ -67,11 +90,27 @@ size_t eags_backward_scratch_bytes(int32_t P) { return scratch_layout(P < 0 ? 0 
 
 int eags_set_option(const char* name, int32_t value) {
     if (name && !strcmp(name, "tma")) { g_opt_tma.store(value ? 1 : 0); return 0; }
+    if (name && !strcmp(name, "kernel_timing")) { g_opt_timing.store(value ? 1 : 0); return 0; }
     return fail(EAGS_ERR_INVALID, "eags_set_option: unknown option");
 }
 int eags_get_option(const char* name, int32_t* value) {
     if (name && value && !strcmp(name, "tma")) { *value = g_opt_tma.load(); return 0; }
+    if (name && value && !strcmp(name, "kernel_timing")) { *value = g_opt_timing.load(); return 0; }
     return fail(EAGS_ERR_INVALID, "eags_get_option: unknown option");
+}
+
+int eags_kernel_times(int32_t max_spans, const char** names, float* ms) {
+    int n = 0;
+    for (TimedSpan& sp : g_spans) {
+        float t = 0.f;
+        cudaEventSynchronize(sp.end);
+        cudaEventElapsedTime(&t, sp.beg, sp.end);
+        if (n < max_spans && names && ms) { names[n] = sp.name; ms[n] = t; n++; }
+        g_event_pool.push_back(sp.beg);
+        g_event_pool.push_back(sp.end);
+    }
+    g_spans.clear();
+    return n;
 }
 
 int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,

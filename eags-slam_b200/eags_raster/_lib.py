@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libeags_raster.so")
+# EAGS_RASTER_LIB selects another build of the same library (A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("EAGS_RASTER_LIB") or os.path.join(_HERE, "libeags_raster.so")
 
 VARIANT_A = 0
 VARIANT_B = 1
@@ -66,6 +67,7 @@ SIGNATURES = {
     "eags_backward_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "eags_set_option": (C.c_int, [C.c_char_p, C.c_int32]),
     "eags_get_option": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32)]),
+    "eags_kernel_times": (C.c_int, [C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]),
     "eags_forward_geom": (C.c_int, [C.POINTER(EagsView), C.POINTER(EagsGaussians), C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_forward_render": (C.c_int, [C.POINTER(EagsView), C.POINTER(EagsGaussians), C.c_void_p,
@@ -118,6 +120,15 @@ def get_option(name: str) -> int:
     v = C.c_int32(0)
     check(load().eags_get_option(name.encode(), C.byref(v)), "eags_get_option")
     return int(v.value)
+
+
+def kernel_times(max_spans: int = 256):
+    """[(launcher name, device ms)] recorded by this thread since the last call (needs the
+    "kernel_timing" option); synchronises with the recorded events."""
+    names = (C.c_char_p * max_spans)()
+    ms = (C.c_float * max_spans)()
+    n = load().eags_kernel_times(max_spans, names, ms)
+    return [(names[i].decode(), float(ms[i])) for i in range(n)]
 
 
 def launch_count() -> int:

@@ -153,8 +153,16 @@ int eags_state_view(const char* what, int32_t P, int32_t width, int32_t height, 
 /* Tuning knobs for A/B measurements (process-wide, read at launch time):
  *   "tma"      1 (default): blend kernels stage splat batches with cp.async.bulk + mbarrier;
  *              0: plain cooperative loads.                                                     */
+/*   "kernel_timing" 1: record CUDA events on the caller's stream around every kernel launcher;
+ *              read them with eags_kernel_times().  Default 0 (no events are ever recorded).    */
 int eags_set_option(const char* name, int32_t value);
 int eags_get_option(const char* name, int32_t* value);
+
+/* Measurement hook (bench.py's live per-kernel roofline): waits for and returns the spans recorded
+ * by the calling thread since the last call -- names[i] is a static string ("preprocess_fwd",
+ * "tile_scan", "duplicate", "sort_pack", "blend_fwd", "blend_bwd", "preprocess_bwd"), ms[i] the
+ * device time of that launcher.  Returns the number of spans written (<= max_spans). */
+int eags_kernel_times(int32_t max_spans, const char** names, float* ms);
 
 /* Number of kernel launches issued by this library in the calling process since load (all
  * threads); bench.py reports the per-step delta as `gpu_launches`. */
