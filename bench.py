@@ -118,6 +118,7 @@ def make_workload(name, device, seed, view_id=0, P=None):
 def run_ours(args):
     import torch.distributed as dist
     from eags_raster import _lib, rasterize as rz, state_array
+    from eags_raster.losses import masked_l1_means
     from gaussian_rasterizer import GaussianRasterizer
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -151,7 +152,11 @@ def run_ours(args):
         color, depth, alpha, radii = raster(means3D=leaf["means3D"], means2D=m2d, opacities=leaf["opacities"],
                                             shs=src["shs"], colors_precomp=None, scales=leaf["scales"],
                                             rotations=leaf["rotations"], cov3D_precomp=None)
-        loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
+        if args.loss == "fused":    # the product's fused loss kernels (eags_raster.losses)
+            lc, ld = masked_l1_means(color, depth, gt_c, gt_d)
+            loss = lc + ld
+        else:                       # the same loss from stock torch ops
+            loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
         loss.backward()
         if world > 1:
             off = 0
@@ -234,7 +239,7 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{wl}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd",
-                       "views_per_step_per_gpu": 1, "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
+                       "views_per_step_per_gpu": 1, "loss": args.loss, "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
                        "l2": "flushed before every timed step (256 MiB write, outside the events)",
                        "parallelism": "1 view/GPU, replica per GPU" + (", NCCL all-reduce of 11 floats/Gaussian" if world > 1 else "")},
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
@@ -441,6 +446,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sync-mode", default=None, choices=["optimistic", "exact", "nosync"])
     ap.add_argument("--tma", type=int, default=None)
+    ap.add_argument("--loss", default="fused", choices=["torch", "fused"],
+                    help="L1 colour + depth loss from torch ops, or the fused loss kernels of eags_raster.losses")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

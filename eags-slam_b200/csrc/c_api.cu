@@ -184,6 +184,33 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
     return 0;
 }
 
+size_t eags_image_l1_scratch_bytes(int32_t W, int32_t H) { return image_l1_scratch_bytes(W, H); }
+
+int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
+                          void* scratch, float* sums4, void* stream) {
+    if (!in || in->width <= 0 || in->height <= 0 || !in->color || !in->depth || !in->gt_color ||
+        !in->gt_depth || !g_color || !g_depth || !scratch || !sums4 || (in->soft_alpha && !in->alpha) ||
+        (long long)in->width * in->height >= (1ll << 30))
+        return fail(EAGS_ERR_INVALID, "eags_image_l1_forward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_image_l1_fwd(in->width, in->height, in->soft_alpha, in->mask_color, in->norm_mode,
+                                     in->eps, in->color, in->depth, in->alpha, in->gt_color, in->gt_depth,
+                                     in->mask, g_color, g_depth, g_alpha, scratch, sums4, s),
+                 "image_l1_fwd");
+    return 0;
+}
+
+int eags_image_l1_backward(int32_t W, int32_t H, const float* sums4, const float* up_color,
+                           const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
+                           void* stream) {
+    if (W <= 0 || H <= 0 || !sums4 || !up_color || !up_depth || !g_color || !g_depth)
+        return fail(EAGS_ERR_INVALID, "eags_image_l1_backward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_image_l1_scale(W, H, sums4, up_color, up_depth, g_color, g_depth, g_alpha, s),
+                 "image_l1_scale");
+    return 0;
+}
+
 int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t capacity,
                     int32_t with_keys, const void* geom_state, const void* image_state,
                     const void* binning_state, const void** ptr, int64_t* count, int32_t* elem_bytes) {

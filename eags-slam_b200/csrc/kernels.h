@@ -83,3 +83,12 @@ int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const Ea
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
                           GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
                           double* pose_acc, cudaStream_t s);
+
+// loss.cu
+size_t image_l1_scratch_bytes(int W, int H);
+int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
+                        const float* color, const float* depth, const float* alpha, const float* gt_color,
+                        const float* gt_depth, const uint8_t* mask, float* g_color, float* g_depth,
+                        float* g_alpha, void* scratch, float* out4, cudaStream_t s);
+int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
+                          float* g_color, float* g_depth, float* g_alpha, cudaStream_t s);

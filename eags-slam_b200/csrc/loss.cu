@@ -1,0 +1,170 @@
+// loss.cu -- fused image-space losses that bracket the rasterizer in every tracking / mapping
+// iteration (reference src/entities/tracker.py:99-128,
+// src/entities/mapper.py:161-165, src/entities/losses.py:8-27).
+//
+// The reference builds these from ~25 elementwise / reduction torch kernels per iteration.  Here:
+//   K9  image_l1_fwd   : ONE pass over the pixels -> the four reductions (colour / depth loss sums and
+//                        their normalisers) and the raw (un-normalised) gradient images
+//                        dL/dcolor, dL/ddepth, dL/dalpha.  Deterministic: per-CTA partials are
+//                        combined in fixed order by the last CTA to finish.
+//   K10 image_l1_scale : scales the raw gradients by upstream_grad / normaliser (device scalars).
+// HBM-bound streaming: 9 floats + 1 mask byte read, 5 floats written per pixel.
+#include "kernels.h"
+
+namespace {
+
+constexpr int LOSS_THREADS = 256;
+
+struct LossArgs {
+    int N;                 // pixels
+    int soft_alpha;        // weight both losses by alpha^3 (tracker.py:118-121)
+    int mask_color;        // apply the mask to the colour loss too (tracker.py:122-125)
+    int norm_mode;         // 0: normalise by #(loss element > 0) (tracker.py:127-128)
+                           // 1: normalise by #masked elements (mean over the mask; mapper.py:161-165, l1_loss)
+    float eps;             // added to |x - y| before weighting (1e-8 in the tracker, 0 for a plain L1)
+    const float* color;    // (3,N)
+    const float* depth;    // (N)
+    const float* alpha;    // (N) or NULL
+    const float* gt_color; // (3,N)
+    const float* gt_depth; // (N)
+    const uint8_t* mask;   // (N) or NULL (all valid)
+    float* g_color;        // (3,N) raw gradient
+    float* g_depth;        // (N)
+    float* g_alpha;        // (N) or NULL
+    double* partial;       // [grid][4]
+    unsigned* ticket;      // zero-initialised by the caller's memset
+    float* out;            // [6] = {colour sum, colour normaliser, depth sum, depth normaliser, colour loss, depth loss}
+};
+
+__device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+image_l1_fwd_kernel(LossArgs a) {
+    float s_c = 0.f, n_c = 0.f, s_d = 0.f, n_d = 0.f;
+    for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < a.N; p += gridDim.x * LOSS_THREADS) {
+        const float m = a.mask ? (a.mask[p] ? 1.f : 0.f) : 1.f;
+        const float al = a.alpha ? a.alpha[p] : 1.f;
+        const float w = a.soft_alpha ? al * al * al : 1.f;
+        const float wc = w * ((a.mask_color || !a.soft_alpha) ? m : 1.f);   // tracker.py:118-125
+        const float wd = w * m;
+        float lc_sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float d = a.color[(size_t)c * a.N + p] - a.gt_color[(size_t)c * a.N + p];
+            const float l = (fabsf(d) + a.eps) * wc;
+            lc_sum += fabsf(d) + a.eps;
+            s_c += l;
+            n_c += (a.norm_mode == 0) ? (l > 0.f ? 1.f : 0.f) : m;
+            a.g_color[(size_t)c * a.N + p] = sgn(d) * wc;
+        }
+        const float dd = a.depth[p] - a.gt_depth[p];
+        const float ld0 = fabsf(dd) + a.eps;
+        const float ld = ld0 * wd;
+        s_d += ld;
+        n_d += (a.norm_mode == 0) ? (ld > 0.f ? 1.f : 0.f) : m;
+        a.g_depth[p] = sgn(dd) * wd;
+        if (a.g_alpha) {
+            // d(alpha^3)/dalpha = 3 alpha^2, applied to the unweighted loss terms it multiplies; the
+            // colour and depth parts are scaled by different factors later, so they are kept apart
+            // in the two halves of a float2-like pair: colour part here, depth part in slot N + p.
+            const float d3 = a.soft_alpha ? 3.f * al * al : 0.f;
+            a.g_alpha[p] = d3 * lc_sum * ((a.mask_color) ? m : 1.f);
+            a.g_alpha[(size_t)a.N + p] = d3 * ld0 * m;
+        }
+    }
+    // block reduction (fixed order inside the block), then a fixed-order pass over the partials
+    __shared__ double sh[4][LOSS_THREADS / 32];
+    double v[4] = {(double)s_c, (double)n_c, (double)s_d, (double)n_d};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        if ((threadIdx.x & 31) == 0) sh[k][threadIdx.x >> 5] = v[k];
+    }
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x < 4) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < LOSS_THREADS / 32; w++) t += sh[threadIdx.x][w];
+        a.partial[(size_t)blockIdx.x * 4 + threadIdx.x] = t;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (last && threadIdx.x < 32) {
+        __threadfence();
+        double t[4] = {0.0, 0.0, 0.0, 0.0};
+        for (unsigned b = threadIdx.x; b < gridDim.x; b += 32)
+#pragma unroll
+            for (int k = 0; k < 4; k++) t[k] += __ldcg(a.partial + (size_t)b * 4 + k);
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t[k] += __shfl_xor_sync(0xffffffffu, t[k], o);
+        if (threadIdx.x == 0) {
+            const float sc = (float)t[0], nc = (float)t[1], sd = (float)t[2], nd = (float)t[3];
+            a.out[0] = sc; a.out[1] = nc; a.out[2] = sd; a.out[3] = nd;
+            a.out[4] = sc / nc;     // 0/0 -> nan, as the reference's division
+            a.out[5] = sd / nd;
+        }
+    }
+}
+
+// g *= up / normaliser; `sums` = the forward's out[4]; `up` = {dL/dcolour_loss, dL/ddepth_loss} (device)
+__global__ void __launch_bounds__(LOSS_THREADS)
+image_l1_scale_kernel(int N, const float* __restrict__ sums, const float* __restrict__ up_c,
+                      const float* __restrict__ up_d, float* __restrict__ g_color,
+                      float* __restrict__ g_depth, float* __restrict__ g_alpha) {
+    const float kc = (sums[1] > 0.f) ? __ldg(up_c) / sums[1] : 0.f;
+    const float kd = (sums[3] > 0.f) ? __ldg(up_d) / sums[3] : 0.f;
+    for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += gridDim.x * LOSS_THREADS) {
+        g_color[p] *= kc;
+        g_color[(size_t)N + p] *= kc;
+        g_color[(size_t)2 * N + p] *= kc;
+        g_depth[p] *= kd;
+        if (g_alpha) g_alpha[p] = g_alpha[p] * kc + g_alpha[(size_t)N + p] * kd;
+    }
+}
+
+int loss_grid(int N) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int want = (N + LOSS_THREADS - 1) / LOSS_THREADS;
+    const int cap = sms * 4;
+    return want < cap ? (want < 1 ? 1 : want) : cap;
+}
+
+}  // namespace
+
+size_t image_l1_scratch_bytes(int W, int H) {
+    (void)W; (void)H;
+    return 256 + (size_t)148 * 8 * 4 * sizeof(double);   // ticket line + partials for up to 1184 CTAs
+}
+
+int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
+                        const float* color, const float* depth, const float* alpha, const float* gt_color,
+                        const float* gt_depth, const uint8_t* mask, float* g_color, float* g_depth,
+                        float* g_alpha, void* scratch, float* out4, cudaStream_t s) {
+    LossArgs a;
+    a.N = W * H; a.soft_alpha = soft_alpha; a.mask_color = mask_color; a.norm_mode = norm_mode; a.eps = eps;
+    a.color = color; a.depth = depth; a.alpha = alpha; a.gt_color = gt_color; a.gt_depth = gt_depth;
+    a.mask = mask; a.g_color = g_color; a.g_depth = g_depth; a.g_alpha = g_alpha;
+    a.ticket = (unsigned*)scratch;
+    a.partial = (double*)((char*)scratch + 256);
+    a.out = out4;
+    int grid = loss_grid(a.N);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (cudaMemsetAsync(scratch, 0, 256, s) != cudaSuccess) return -1;
+    image_l1_fwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(a);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
+                          float* g_color, float* g_depth, float* g_alpha, cudaStream_t s) {
+    const int N = W * H;
+    image_l1_scale_kernel<<<loss_grid(N), LOSS_THREADS, 0, s>>>(N, sums, up_c, up_d, g_color, g_depth, g_alpha);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}

@@ -56,6 +56,15 @@ class EagsInputGrads(C.Structure):
     ]
 
 
+class EagsImageL1(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("soft_alpha", C.c_int32), ("mask_color", C.c_int32),
+        ("norm_mode", C.c_int32), ("eps", C.c_float),
+        ("color", C.c_void_p), ("depth", C.c_void_p), ("alpha", C.c_void_p), ("gt_color", C.c_void_p),
+        ("gt_depth", C.c_void_p), ("mask", C.c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); also the list tests/test_abi.py checks against include/eags_raster.h
 SIGNATURES = {
     "eags_abi_version": (C.c_int, []),
@@ -77,6 +86,11 @@ SIGNATURES = {
                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                 C.POINTER(EagsImageGrads), C.POINTER(EagsInputGrads), C.c_void_p,
                                 C.c_void_p]),
+    "eags_image_l1_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "eags_image_l1_forward": (C.c_int, [C.POINTER(EagsImageL1), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]),
+    "eags_image_l1_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_state_view": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p),
                                   C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),

@@ -1,0 +1,114 @@
+"""Fused image-space losses for the tracking / mapping iterations.
+
+Drop-in equivalents of what the reference computes with ~25 small torch kernels per iteration:
+
+* :func:`tracking_losses` -- src/entities/tracker.py:112-128: ``|x - y| + 1e-8`` per element, the
+  depth-validity / alpha / outlier ``tracking_mask``, optional ``alpha**3`` weighting, each of the two
+  sums divided by its number of positive elements.
+* :func:`masked_l1_means` -- the two L1 means of a mapping iteration, src/entities/mapper.py:161-165
+  with src/entities/losses.py:8-27 (``l1_loss(image[:, mask], gt[:, mask])``, ``l1_loss(depth[:, mask],
+  gt_depth[mask])``); with ``mask=None`` they are plain means (the benchmark's loss).
+
+Both return ``(color_loss, depth_loss)`` as 0-d tensors with autograd to ``color``, ``depth`` (and
+``alpha``).  One CUDA kernel produces the four reductions and the raw gradient images, one more scales
+them in ``backward`` -- no host synchronisation anywhere.  CUDA tensors only (no CPU path).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+
+def _c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.to(torch.float32).contiguous()
+    return t
+
+
+class _ImageL1(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, color, depth, alpha, gt_color, gt_depth, mask, soft_alpha, mask_color, norm_mode, eps):
+        lib = _lib.load()
+        if not color.is_cuda:
+            raise RuntimeError("eags_raster.losses: tensors must live on a CUDA device (there is no CPU path)")
+        dev = color.device
+        H, W = int(color.shape[-2]), int(color.shape[-1])
+        with torch.cuda.device(dev):
+            color, depth, gt_color, gt_depth = _c(color), _c(depth), _c(gt_color), _c(gt_depth)
+            if color.numel() != 3 * H * W or depth.numel() != H * W or gt_color.numel() != 3 * H * W or \
+                    gt_depth.numel() != H * W:
+                raise ValueError("expected color (3,H,W), depth (1,H,W) and matching ground truth")
+            alpha_c = _c(alpha) if alpha is not None else None
+            if soft_alpha and alpha_c is None:
+                raise ValueError("soft_alpha needs the alpha image")
+            mask_c = None
+            if mask is not None:
+                mask_c = mask.reshape(H, W).to(torch.uint8).contiguous()
+            want_alpha_grad = bool(soft_alpha and alpha is not None and ctx.needs_input_grad[2])
+            f32 = dict(dtype=torch.float32, device=dev)
+            g_color = torch.empty(3, H, W, **f32)
+            g_depth = torch.empty(1, H, W, **f32)
+            g_alpha = torch.empty(2, H, W, **f32) if want_alpha_grad else None
+            sums = torch.empty(6, **f32)
+            scratch = torch.empty(lib.eags_image_l1_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
+            args = _lib.EagsImageL1(W, H, int(bool(soft_alpha)), int(bool(mask_color)), int(norm_mode), float(eps),
+                                    color.data_ptr(), depth.data_ptr(),
+                                    None if alpha_c is None else alpha_c.data_ptr(), gt_color.data_ptr(),
+                                    gt_depth.data_ptr(), None if mask_c is None else mask_c.data_ptr())
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.eags_image_l1_forward(C.byref(args), g_color.data_ptr(), g_depth.data_ptr(),
+                                                 None if g_alpha is None else g_alpha.data_ptr(),
+                                                 scratch.data_ptr(), sums.data_ptr(), stream),
+                       "eags_image_l1_forward")
+            # loss = sum / normaliser, formed by the kernel (0/0 -> nan exactly as the reference's division)
+            color_loss, depth_loss = sums[4], sums[5]
+        ctx.save_for_backward(sums, g_color, g_depth, g_alpha if g_alpha is not None else torch.empty(0))
+        ctx.shape = (H, W)
+        ctx.alpha_shape = None if alpha is None else alpha.shape
+        ctx.shapes = (color.shape, depth.shape)
+        return color_loss, depth_loss
+
+    @staticmethod
+    def backward(ctx, up_color, up_depth):
+        lib = _lib.load()
+        sums, g_color, g_depth, g_alpha = ctx.saved_tensors
+        H, W = ctx.shape
+        dev = sums.device
+        with torch.cuda.device(dev):
+            zero = None
+            if up_color is None or up_depth is None:
+                zero = torch.zeros((), dtype=torch.float32, device=dev)
+            up_color = _c(up_color) if up_color is not None else zero
+            up_depth = _c(up_depth) if up_depth is not None else zero
+            ga = g_alpha if g_alpha.numel() else None
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            # the raw gradients are scaled in place: a second backward through the same node is not supported
+            _lib.check(lib.eags_image_l1_backward(W, H, sums.data_ptr(), up_color.data_ptr(), up_depth.data_ptr(),
+                                                  g_color.data_ptr(), g_depth.data_ptr(),
+                                                  None if ga is None else ga.data_ptr(), stream),
+                       "eags_image_l1_backward")
+        d_alpha = None
+        if ga is not None:
+            d_alpha = ga[0].view(ctx.alpha_shape)
+        return (g_color.view(ctx.shapes[0]), g_depth.view(ctx.shapes[1]), d_alpha, None, None, None, None, None,
+                None, None)
+
+
+def tracking_losses(color: torch.Tensor, depth: torch.Tensor, alpha: torch.Tensor, gt_color: torch.Tensor,
+                    gt_depth: torch.Tensor, tracking_mask: Optional[torch.Tensor], soft_alpha: bool = True,
+                    mask_invalid_depth_in_color_loss: bool = False, eps: float = 1e-8
+                    ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``color_loss, depth_loss`` of reference tracker.py:116-128 (``tracking_mask`` as built at :102-113)."""
+    return _ImageL1.apply(color, depth, alpha, gt_color, gt_depth, tracking_mask, bool(soft_alpha),
+                          bool(mask_invalid_depth_in_color_loss), 0, float(eps))
+
+
+def masked_l1_means(color: torch.Tensor, depth: torch.Tensor, gt_color: torch.Tensor, gt_depth: torch.Tensor,
+                    mask: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``l1_loss(color[:, mask], gt_color[:, mask]), l1_loss(depth[:, mask], gt_depth[mask])`` of reference
+    mapper.py:161-165; plain means when ``mask`` is None."""
+    return _ImageL1.apply(color, depth, None, gt_color, gt_depth, mask, False, False, 1, 0.0)

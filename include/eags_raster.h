@@ -138,6 +138,35 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
                   int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
                   void* scratch, void* stream);
 
+/* ---- Fused image-space losses ---------------------------------------------
+ * The per-iteration losses that bracket the rasterizer in the reference: the tracking loss
+ * (src/entities/tracker.py:99-128: |x - y| + eps, depth-valid mask, alpha^3 weighting, each sum
+ * divided by its number of positive elements) and the masked L1 means of mapping
+ * (src/entities/mapper.py:161-165 with src/entities/losses.py:8-27).  One pass produces
+ * sums = {colour sum, colour normaliser, depth sum, depth normaliser, colour loss, depth loss} (6
+ * floats, loss = sum / normaliser) and the raw gradient images;
+ * eags_image_l1_backward scales them by upstream_grad / normaliser (device scalars, no host sync). */
+typedef struct EagsImageL1 {
+    int32_t width, height;
+    int32_t soft_alpha;    /* weight by alpha^3 (tracker.py:118-121)                               */
+    int32_t mask_color;    /* mask the colour loss as well (tracker.py:122-125)                    */
+    int32_t norm_mode;     /* 0: divide by #(element > 0) (tracker.py:127-128); 1: by #masked      */
+    float eps;             /* 1e-8 in the tracker, 0 for a plain L1                                */
+    const float* color;    /* (3,H,W) */
+    const float* depth;    /* (1,H,W) */
+    const float* alpha;    /* (1,H,W) or NULL */
+    const float* gt_color; /* (3,H,W) */
+    const float* gt_depth; /* (1,H,W) */
+    const uint8_t* mask;   /* (H,W) 0/1 or NULL */
+} EagsImageL1;
+size_t eags_image_l1_scratch_bytes(int32_t width, int32_t height);
+/* g_color (3,H,W), g_depth (1,H,W), g_alpha (2,H,W) or NULL, sums4 (SIX floats): device, caller-owned */
+int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
+                          void* scratch, float* sums4, void* stream);
+int eags_image_l1_backward(int32_t width, int32_t height, const float* sums4, const float* up_color,
+                           const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
+                           void* stream);
+
 /* Introspection of the state buffers (parity tests, debugging).  `what` selects the array; the
  * function returns its device address, element count and element size.  Names:
  *   "xy" float2[P], "conic_opacity" float4[P], "rgbd" float4[P] (r,g,b,depth),
