@@ -141,9 +141,14 @@ def run_ours(args):
     devt = {k: sc[k].to(dev) for k in keys + ("shs",)}
     gt_c, gt_d = sc["gt_color"].to(dev), sc["gt_depth"].to(dev)
     raster = GaussianRasterizer(raster_settings=settings)
-    # fused gradient buffer: 13 floats / Gaussian (xyz 3, scale 3, rot 4, opacity 1, +2 pad-free)
+    # sharded mapping (N > 1): p.grad of every leaf is a view into ONE fused buffer of 11 floats /
+    # Gaussian (xyz 3, scale 3, rot 4, opacity 1) -> one NCCL all-reduce per step, nothing packed
     sizes = {"means3D": 3, "scales": 3, "rotations": 4, "opacities": 1}
     flat_grad = torch.zeros(P * 11, device=dev)
+    grad_views, off = {}, 0
+    for k in keys:
+        grad_views[k] = flat_grad[off:off + P * sizes[k]].view(P, sizes[k])
+        off += P * sizes[k]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def step(src, read_loss=False):
@@ -157,14 +162,13 @@ def run_ours(args):
             loss = lc + ld
         else:                       # the same loss from stock torch ops
             loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
-        loss.backward()
         if world > 1:
-            off = 0
-            for k in keys:
-                n = P * sizes[k]
-                flat_grad[off:off + n].copy_(leaf[k].grad.reshape(-1))
-                off += n
+            # the backward kernel writes the 11 floats / Gaussian straight into the fused buffer
+            with rz.grad_arena(**grad_views):
+                loss.backward()
             dist.all_reduce(flat_grad)
+        else:
+            loss.backward()
         return float(loss.detach()) if read_loss else loss
 
     def barrier():

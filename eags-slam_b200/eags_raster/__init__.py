@@ -8,6 +8,7 @@ from . import _lib  # noqa: F401
 from .rasterize import (  # noqa: F401
     RasterState,
     get_sync_mode,
+    grad_arena,
     rasterize_backward,
     rasterize_forward,
     rasterize_gaussians,

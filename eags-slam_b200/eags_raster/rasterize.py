@@ -52,6 +52,34 @@ def reserve_capacity(device, num_keys: int) -> None:
     _capacity[idx] = max(_capacity.get(idx, 0), int(num_keys))
 
 
+_arena = None
+
+
+class grad_arena:
+    """Context manager: while active, the backward pass writes the gradients of the named operator
+    inputs straight into caller-provided tensors (e.g. slices of one fused all-reduce buffer,
+    :class:`eags_raster.sharded.FusedGradBucket`) instead of fresh allocations, so a following
+    collective needs no packing.  Valid for ONE backward per activation (a second backward would
+    overwrite the first result) and process-wide (do not run another rasterizer backward concurrently
+    on a second thread while it is active); keys: means3D, scales, rotations, opacities, shs, colors_precomp,
+    cov3D_precomp, means2D."""
+
+    def __init__(self, **tensors):
+        self.tensors = tensors
+
+    def __enter__(self):
+        # process-wide, not thread-local: autograd runs backward() on its own device thread
+        global _arena
+        self.prev = _arena
+        _arena = self.tensors
+        return self
+
+    def __exit__(self, *exc):
+        global _arena
+        _arena = self.prev
+        return False
+
+
 class RasterState(NamedTuple):
     """Everything the backward pass (and the parity tests) need from a forward pass."""
     P: int
@@ -266,15 +294,26 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
             dL_dcolor = torch.zeros(3, H, W, **f32)
         if dL_ddepth is None:
             dL_ddepth = torch.zeros(1, H, W, **f32)
+        arena = _arena or {}
+
+        def buf(name, *shape):
+            t = arena.get(name)
+            if t is not None:
+                if t.dtype != torch.float32 or not t.is_contiguous() or t.device != device or \
+                        t.numel() != torch.Size(shape).numel():
+                    raise ValueError(f"grad_arena['{name}'] must be a contiguous fp32 tensor of shape {shape} on {device}")
+                return t.view(*shape)
+            return torch.empty(*shape, **f32)
+
         out = dict(
-            means3D=torch.empty(P, 3, **f32),
-            means2D=torch.empty(P, 3, **f32),
-            opacities=torch.empty(P, 1, **f32),
-            shs=torch.empty(P, M, 3, **f32) if (shs is not None and want_shs) else None,
-            colors_precomp=torch.empty(P, 3, **f32) if colors_precomp is not None else None,
-            scales=torch.empty(P, 3, **f32) if scales is not None else None,
-            rotations=torch.empty(P, 4, **f32) if rotations is not None else None,
-            cov3D_precomp=torch.empty(P, 6, **f32) if cov3D_precomp is not None else None,
+            means3D=buf("means3D", P, 3),
+            means2D=buf("means2D", P, 3),
+            opacities=buf("opacities", P, 1),
+            shs=buf("shs", P, M, 3) if (shs is not None and want_shs) else None,
+            colors_precomp=buf("colors_precomp", P, 3) if colors_precomp is not None else None,
+            scales=buf("scales", P, 3) if scales is not None else None,
+            rotations=buf("rotations", P, 4) if rotations is not None else None,
+            cov3D_precomp=buf("cov3D_precomp", P, 6) if cov3D_precomp is not None else None,
             tau=torch.empty(6, **f32) if want_tau else None,
         )
         stream = torch.cuda.current_stream(device).cuda_stream

@@ -182,3 +182,47 @@ def test_variant_b_pose_gradient_through_theta_rho():
     assert screenspace.grad is not None
     vis = radii > 0
     assert int(n_touched[~vis].sum()) == 0
+
+
+def test_grad_arena_writes_into_fused_bucket():
+    """eags_raster.grad_arena: the backward kernel writes the per-Gaussian gradients straight into
+    slices of one flat buffer (the all-reduce bucket of sharded mapping) -- same values, no copies."""
+    import eags_raster
+    from gaussian_rasterizer import GaussianRasterizer
+    sc = scene.make_scene("ragged", P=1800, seed=21)
+    cam = scene.workload_camera("ragged")
+    s = _settings_a(cam)
+    keys = ("means3D", "scales", "rotations", "opacities")
+    sizes = {"means3D": 3, "scales": 3, "rotations": 4, "opacities": 1}
+    P = 1800
+
+    def run(arena):
+        leaf = {k: sc[k].to(DEV).requires_grad_(True) for k in keys}
+        out = GaussianRasterizer(raster_settings=s)(
+            means3D=leaf["means3D"], means2D=torch.zeros_like(leaf["means3D"], requires_grad=True),
+            opacities=leaf["opacities"], colors_precomp=None, shs=sc["shs"].to(DEV), scales=leaf["scales"],
+            rotations=leaf["rotations"], cov3D_precomp=None)
+        loss = out[0].sum() + 0.3 * out[1].sum()
+        if arena is None:
+            loss.backward()
+        else:
+            with eags_raster.grad_arena(**arena):
+                loss.backward()
+        return leaf
+
+    ref = run(None)
+    flat = torch.full((P * 11,), float("nan"), device=DEV)
+    views, off = {}, 0
+    for k in keys:
+        views[k] = flat[off:off + P * sizes[k]].view(P, sizes[k])
+        off += P * sizes[k]
+    got = run(views)
+    assert torch.isfinite(flat).all()
+    off = 0
+    for k in keys:
+        assert rel_err(got[k].grad.cpu().numpy(), ref[k].grad.cpu().numpy()) < 1e-5
+        assert torch.equal(flat[off:off + P * sizes[k]].view(P, sizes[k]), got[k].grad)
+        assert got[k].grad.untyped_storage().data_ptr() == flat.untyped_storage().data_ptr()   # stolen view, no copy
+        off += P * sizes[k]
+    with pytest.raises(ValueError, match="grad_arena"):
+        run(dict(means3D=torch.zeros(5, 3, device=DEV)))
