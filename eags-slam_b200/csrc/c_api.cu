@@ -169,7 +169,7 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
         if (gout->dL_dtau) CHECK_CUDA(cudaMemsetAsync(gout->dL_dtau, 0, 6 * sizeof(float), s), "memset(dtau)");
         return 0;
     }
-    if (!radii || !geom_state || !image_state || !binning_state || !scratch || !gout->dL_dmeans3D)
+    if (!radii || !geom_state || !image_state || !binning_state || !scratch)
         return fail(EAGS_ERR_INVALID, "eags_backward: null buffer");
     const int W = view->image_width, H = view->image_height;
     ImagePtrs img = image_ptrs(const_cast<void*>(image_state), W, H);
@@ -181,6 +181,26 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
     CHECK_CUDA(cudaMemsetAsync(scratch, 0, SL.pose + 256, s), "memset(scratch)");
     CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, (unsigned*)((char*)scratch + SL.pose + 128), g_opt_tma.load(), s), "blend_bwd");
     CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, s), "preprocess_bwd");
+    return 0;
+}
+
+int eags_pose_compose(const float* q, const float* t, const float* viewmatrix, const float* projmatrix,
+                      const float* campos, float* viewmatrix_out, float* projmatrix_out,
+                      float* campos_out, void* stream) {
+    if (!q || !t || !viewmatrix || !projmatrix || !campos || !viewmatrix_out || !projmatrix_out || !campos_out)
+        return fail(EAGS_ERR_INVALID, "eags_pose_compose: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_pose_compose(q, t, viewmatrix, projmatrix, campos, viewmatrix_out, projmatrix_out,
+                                     campos_out, s), "pose_compose");
+    return 0;
+}
+
+int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, const float* dL_dtau,
+                    float* dL_dq, float* dL_dt, void* stream) {
+    if (!q || !t || !viewmatrix || !dL_dtau || !dL_dq || !dL_dt)
+        return fail(EAGS_ERR_INVALID, "eags_pose_chain: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_pose_chain(q, t, viewmatrix, dL_dtau, dL_dq, dL_dt, s), "pose_chain");
     return 0;
 }
 

@@ -92,3 +92,10 @@ int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_m
                         float* g_alpha, void* scratch, float* out4, cudaStream_t s);
 int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
                           float* g_color, float* g_depth, float* g_alpha, cudaStream_t s);
+
+// pose.cu
+int launch_pose_compose(const float* q, const float* t, const float* view, const float* proj,
+                        const float* campos, float* view_out, float* proj_out, float* campos_out,
+                        cudaStream_t s);
+int launch_pose_chain(const float* q, const float* t, const float* view, const float* dtau, float* dq,
+                      float* dt, cudaStream_t s);

@@ -508,7 +508,7 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
 #pragma unroll
             for (int k = 0; k < 3; k++) dm[k] = dmean_cov[k] + dmean_proj[k] + dmean_dep[k] + dmean_sh[k];
             // Sigma -> scale, rotation
-            if (!a.cov3D_precomp) {
+            if (!a.cov3D_precomp && (b.dscales || b.drotations)) {
                 const float4 q = *reinterpret_cast<const float4*>(a.rotations + (size_t)4 * i);
                 float R[3][3];
                 quat_to_R(q, R);
@@ -569,7 +569,9 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             for (int m = 0; m < a.M * 3; m++) dsh[m] = 0.f;
         }
         // stores (all P rows are written: the binding hands in torch.empty buffers)
-        b.dmeans3D[(size_t)3 * i] = dm[0]; b.dmeans3D[(size_t)3 * i + 1] = dm[1]; b.dmeans3D[(size_t)3 * i + 2] = dm[2];
+        if (b.dmeans3D) {
+            b.dmeans3D[(size_t)3 * i] = dm[0]; b.dmeans3D[(size_t)3 * i + 1] = dm[1]; b.dmeans3D[(size_t)3 * i + 2] = dm[2];
+        }
         if (b.dmeans2D) {
             b.dmeans2D[(size_t)3 * i] = g2x; b.dmeans2D[(size_t)3 * i + 1] = g2y; b.dmeans2D[(size_t)3 * i + 2] = 0.f;
         }

@@ -91,6 +91,8 @@ SIGNATURES = {
                                         C.c_void_p, C.c_void_p]),
     "eags_image_l1_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "eags_pose_compose": (C.c_int, [C.c_void_p] * 9),
+    "eags_pose_chain": (C.c_int, [C.c_void_p] * 7),
     "eags_state_view": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p),
                                   C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),

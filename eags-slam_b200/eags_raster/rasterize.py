@@ -272,9 +272,10 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
 
 def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, colors_precomp, scales,
                        rotations, cov3D_precomp, dL_dcolor, dL_ddepth, dL_dthird=None,
-                       want_shs=True, want_tau=False):
+                       want_shs=True, want_tau=False, pose_only=False):
     """Returns dict(means3D, means2D, opacities, shs | colors_precomp, scales, rotations |
-    cov3D_precomp, tau)."""
+    cov3D_precomp, tau).  ``pose_only``: only ``tau`` is produced -- no per-Gaussian gradient array is
+    allocated or written (the tracking fast path, eags_raster.tracking)."""
     lib = _lib.load()
     device = state.radii.device
     P, M, H, W = state.P, state.M, state.H, state.W
@@ -315,7 +316,9 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
             rotations=buf("rotations", P, 4) if rotations is not None else None,
             cov3D_precomp=buf("cov3D_precomp", P, 6) if cov3D_precomp is not None else None,
             tau=torch.empty(6, **f32) if want_tau else None,
-        )
+        ) if not pose_only else dict(
+            means3D=None, means2D=None, opacities=None, shs=None, colors_precomp=None, scales=None,
+            rotations=None, cov3D_precomp=None, tau=torch.empty(6, **f32))
         stream = torch.cuda.current_stream(device).cuda_stream
         view, keep = _make_view(settings, state.variant, device)
         g = _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations,

@@ -1,0 +1,99 @@
+"""Tracking fast path: render under an optimisable relative camera pose without touching the
+Gaussians.
+
+The reference's tracking iteration (src/entities/tracker.py:85-97) builds ``rel_transform`` from a
+quaternion + translation, moves ALL P means and left-multiplies ALL P rotations in PyTorch, renders
+them with ``render_gaussian_model(override_means_3d=..., override_rotations=...)`` from the fixed
+previous camera, and gets the pose gradient by autograd through ``dL/dmeans3D`` (P,3) and
+``dL/drotations`` (P,4): ~40 P-sized torch kernels per iteration.  Rendering the moved Gaussians
+from camera ``L`` equals rendering the original ones from camera ``L @ Rel``, so here
+
+    color, depth, alpha, radii = render_relative(settings, means3D, opacities, shs, scales, rotations,
+                                                 cam_rot, cam_trans)
+
+folds the pose into the view matrices (one tiny kernel), renders with the ordinary kernels, and in
+backward turns the rasterizer's own camera-pose gradient ``dL/dtau`` into ``cam_rot.grad`` (4,) and
+``cam_trans.grad`` (3,) (one tiny kernel).  The per-Gaussian gradient arrays are never written.
+
+Same image as the reference path up to fp32 rounding (the pose is applied once to the camera instead
+of P times to the points).  SH degree must be 0 -- what every call site of the reference uses
+(utils.py:77,114): the reference evaluates view-dependent SH in the *moved* frame, which this
+formulation does not reproduce.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from types import SimpleNamespace
+
+import torch
+
+from . import _lib
+from .rasterize import _f32c, rasterize_backward, rasterize_forward
+
+
+def compose_settings(settings, cam_rot: torch.Tensor, cam_trans: torch.Tensor):
+    """Settings of the camera ``L @ Rel(cam_rot, cam_trans)``; also returns the contiguous originals."""
+    lib = _lib.load()
+    device = cam_rot.device
+    with torch.cuda.device(device):
+        vm = _f32c(settings.viewmatrix, device)
+        pm = _f32c(settings.projmatrix, device)
+        cp = _f32c(settings.campos, device)
+        q = _f32c(cam_rot.detach().reshape(-1), device)
+        t = _f32c(cam_trans.detach().reshape(-1), device)
+        if q.numel() != 4 or t.numel() != 3:
+            raise ValueError("cam_rot must have 4 elements (wxyz) and cam_trans 3")
+        out = torch.empty(35, dtype=torch.float32, device=device)
+        stream = torch.cuda.current_stream(device).cuda_stream
+        _lib.check(lib.eags_pose_compose(q.data_ptr(), t.data_ptr(), vm.data_ptr(), pm.data_ptr(), cp.data_ptr(),
+                                         out.data_ptr(), out.data_ptr() + 64, out.data_ptr() + 128, stream),
+                   "eags_pose_compose")
+    s2 = SimpleNamespace(
+        image_height=settings.image_height, image_width=settings.image_width, tanfovx=settings.tanfovx,
+        tanfovy=settings.tanfovy, bg=settings.bg, scale_modifier=settings.scale_modifier,
+        viewmatrix=out[:16].view(4, 4), projmatrix=out[16:32].view(4, 4), sh_degree=settings.sh_degree,
+        campos=out[32:35], prefiltered=settings.prefiltered, debug=settings.debug,
+        projmatrix_raw=getattr(settings, "projmatrix_raw", None))
+    return s2, (q, t, vm)
+
+
+class _RenderRelative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cam_rot, cam_trans, means3D, opacities, shs, scales, rotations, settings):
+        if not means3D.is_cuda:
+            raise RuntimeError("eags_raster.tracking: tensors must live on a CUDA device (there is no CPU path)")
+        if int(settings.sh_degree) != 0:
+            raise ValueError("render_relative supports sh_degree == 0 only (see the module docstring)")
+        s2, (q, t, vm) = compose_settings(settings, cam_rot, cam_trans)
+        color, depth, alpha, radii, _, state = rasterize_forward(
+            s2, _lib.VARIANT_A, means3D, opacities, shs=shs, scales=scales, rotations=rotations)
+        ctx.s2, ctx.state, ctx.pose = s2, state, (q, t, vm)
+        ctx.shapes = (cam_rot.shape, cam_trans.shape)
+        ctx.save_for_backward(means3D, opacities, shs, scales, rotations)
+        ctx.mark_non_differentiable(radii)
+        return color, depth, alpha, radii
+
+    @staticmethod
+    def backward(ctx, g_color, g_depth, g_alpha, _unused):
+        lib = _lib.load()
+        means3D, opacities, shs, scales, rotations = ctx.saved_tensors
+        q, t, vm = ctx.pose
+        device = q.device
+        if ctx.state.P == 0:
+            return (torch.zeros(ctx.shapes[0], device=device), torch.zeros(ctx.shapes[1], device=device),
+                    None, None, None, None, None, None)
+        out = rasterize_backward(ctx.s2, ctx.state, means3D, opacities, shs, None, scales, rotations, None,
+                                 g_color, g_depth, g_alpha, want_shs=False, want_tau=True, pose_only=True)
+        with torch.cuda.device(device):
+            g = torch.empty(7, dtype=torch.float32, device=device)
+            stream = torch.cuda.current_stream(device).cuda_stream
+            _lib.check(lib.eags_pose_chain(q.data_ptr(), t.data_ptr(), vm.data_ptr(), out["tau"].data_ptr(),
+                                           g.data_ptr(), g.data_ptr() + 16, stream), "eags_pose_chain")
+        return g[:4].view(ctx.shapes[0]), g[4:].view(ctx.shapes[1]), None, None, None, None, None, None
+
+
+def render_relative(settings, means3D, opacities, shs, scales, rotations, cam_rot, cam_trans):
+    """Variant-A render of (means3D, ..., rotations) moved by the relative pose (cam_rot wxyz, un-normalised
+    as ``opt_cam_rot`` in tracker.py:85; cam_trans) seen from ``settings``' camera.  Returns
+    ``(color, depth, alpha, radii)``; gradients flow to ``cam_rot`` and ``cam_trans`` only."""
+    return _RenderRelative.apply(cam_rot, cam_trans, means3D, opacities, shs, scales, rotations, settings)

@@ -90,8 +90,8 @@ typedef struct EagsImageGrads {
 } EagsImageGrads;
 
 /* Gradients w.r.t. the operator inputs (outputs of the backward pass).  Any pointer may be NULL
- * (that gradient is skipped) except dL_dmeans3D.  All are fully written (zeros for culled
- * Gaussians). */
+ * (that gradient is skipped; with only dL_dtau set the per-Gaussian scale / rotation / SH backward
+ * is not even computed).  Non-NULL arrays are fully written (zeros for culled Gaussians). */
 typedef struct EagsInputGrads {
     float* dL_dmeans3D;        /* (P,3) */
     float* dL_dmeans2D;        /* (P,3) screen-space gradient (x,y,0): lands in means2D.grad   */
@@ -166,6 +166,19 @@ int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth,
 int eags_image_l1_backward(int32_t width, int32_t height, const float* sums4, const float* up_color,
                            const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
                            void* stream);
+
+/* ---- Tracking fast path ----------------------------------------
+ * Replaces the P-sized pose transform + its autograd of src/entities/tracker.py:85-97 by folding the
+ * optimisable relative pose (quaternion q wxyz, un-normalised; translation t) into the view matrices:
+ * rendering R(q) p + t, q (x) r from camera L equals rendering p, r from camera L * Rel.
+ * eags_pose_compose writes viewmatrix' / projmatrix' / campos' (device, 16/16/3 floats);
+ * eags_pose_chain turns the rasterizer's dL_dtau (6) into dL/dq (4) and dL/dt (3).  `viewmatrix`,
+ * `projmatrix`, `campos` are the ORIGINAL settings (the previous camera, utils.py:95-104). */
+int eags_pose_compose(const float* q, const float* t, const float* viewmatrix, const float* projmatrix,
+                      const float* campos, float* viewmatrix_out, float* projmatrix_out,
+                      float* campos_out, void* stream);
+int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, const float* dL_dtau,
+                    float* dL_dq, float* dL_dt, void* stream);
 
 /* Introspection of the state buffers (parity tests, debugging).  `what` selects the array; the
  * function returns its device address, element count and element size.  Names:
