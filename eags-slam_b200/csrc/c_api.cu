@@ -231,6 +231,32 @@ int eags_image_l1_backward(int32_t W, int32_t H, const float* sums4, const float
     return 0;
 }
 
+size_t eags_neighbors_workspace_bytes(int64_t n_ref) { return neighbors_workspace_bytes(n_ref); }
+
+int eags_knn_mean_dist2(const float* points, int32_t n, float* out, void* workspace,
+                        size_t workspace_bytes, void* stream) {
+    if (n < 0 || (n > 0 && (!points || !out || !workspace)) ||
+        workspace_bytes < neighbors_workspace_bytes(n))
+        return fail(EAGS_ERR_INVALID, "eags_knn_mean_dist2: bad argument or workspace too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_knn_mean_dist2(points, n, out, workspace, s), "knn_mean_dist2");
+    return 0;
+}
+
+int eags_radius_has_neighbor(const float* ref_points, int32_t n_ref, const float* query_points,
+                             int32_t n_query, float radius, uint8_t* has_neighbor, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+    if (n_ref < 0 || n_query < 0 || (n_query > 0 && (!query_points || !has_neighbor)) ||
+        (n_ref > 0 && n_query > 0 && (!ref_points || !workspace)) ||
+        (n_ref > 0 && workspace_bytes < neighbors_workspace_bytes(n_ref)))
+        return fail(EAGS_ERR_INVALID, "eags_radius_has_neighbor: bad argument or workspace too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_radius_has_neighbor(ref_points, n_ref, query_points, n_query, radius, has_neighbor,
+                                            workspace, s),
+                 "radius_has_neighbor");
+    return 0;
+}
+
 int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t capacity,
                     int32_t with_keys, const void* geom_state, const void* image_state,
                     const void* binning_state, const void** ptr, int64_t* count, int32_t* elem_bytes) {

@@ -99,3 +99,9 @@ int launch_pose_compose(const float* q, const float* t, const float* view, const
                         cudaStream_t s);
 int launch_pose_chain(const float* q, const float* t, const float* view, const float* dtau, float* dq,
                       float* dt, cudaStream_t s);
+
+// knn.cu
+size_t neighbors_workspace_bytes(long long n_ref);
+int launch_knn_mean_dist2(const float* pts, int n, float* out, void* ws, cudaStream_t s);
+int launch_radius_has_neighbor(const float* ref, int n_ref, const float* query, int n_query,
+                               float radius2, uint8_t* has_neighbor, void* ws, cudaStream_t s);

@@ -180,6 +180,23 @@ int eags_pose_compose(const float* q, const float* t, const float* viewmatrix, c
 int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, const float* dL_dtau,
                     float* dL_dq, float* dL_dt, void* stream);
 
+/* ---- Neighbour queries around keyframe seeding -------------------------------
+ * eags_knn_mean_dist2 replaces `simple_knn._C.distCUDA2(points)` (un-vendored pip dependency
+ * `simple-knn`; reference call sites src/entities/gaussian_model.py:143,146,253,257,298,301,616):
+ * out[i] = mean of the squared distances from point i to its 3 nearest other points (FLT_MAX
+ * stand-ins when fewer than 4 points exist, as upstream).  points (n,3) fp32, out (n,) fp32.
+ * eags_radius_has_neighbor replaces the faiss IndexFlatL2 search of
+ * src/utils/mapper_utils.py:193-226 (compute_new_points_ids): has_neighbor[q] = 1 iff some reference
+ * point has SQUARED distance < radius (the reference compares faiss' squared distances with
+ * `radius` directly).  Both build a hashed uniform grid in `workspace` (device, caller-owned,
+ * eags_neighbors_workspace_bytes(n_ref) bytes; n_ref = n for the k-NN query); exact results. */
+size_t eags_neighbors_workspace_bytes(int64_t n_ref);
+int eags_knn_mean_dist2(const float* points, int32_t n, float* out, void* workspace,
+                        size_t workspace_bytes, void* stream);
+int eags_radius_has_neighbor(const float* ref_points, int32_t n_ref, const float* query_points,
+                             int32_t n_query, float radius, uint8_t* has_neighbor, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
 /* Introspection of the state buffers (parity tests, debugging).  `what` selects the array; the
  * function returns its device address, element count and element size.  Names:
  *   "xy" float2[P], "conic_opacity" float4[P], "rgbd" float4[P] (r,g,b,depth),
