@@ -156,10 +156,39 @@ int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int3
     return 0;
 }
 
+static bool route_ok(const EagsPeerRoute* r, int64_t P) {
+    if (!r || r->world < 1 || r->world > EAGS_MAX_PEERS || r->rank < 0 || r->rank >= r->world || r->P != P)
+        return false;
+    for (int k = 0; k < r->world; k++)
+        if (!r->recv[k] || !r->reduced[k] || !r->flags[k]) return false;
+    return true;
+}
+
 int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
                   const void* geom_state, const void* image_state, const void* binning_state,
                   int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
                   void* scratch, void* stream) {
+    return eags_backward_routed(view, g, radii, geom_state, image_state, binning_state, capacity, gin, gout,
+                                scratch, nullptr, stream);
+}
+
+size_t eags_peer_flags_bytes(void) { return peer_flags_bytes(); }
+
+int eags_peer_reduce(const EagsPeerRoute* route, uint32_t epoch, float scale, int32_t wait, void* stream) {
+    if (!route || !route_ok(route, route->P) || route->P < 0)
+        return fail(EAGS_ERR_INVALID, "eags_peer_reduce: bad route");
+    if (route->P == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_peer_reduce(*route, epoch, scale, wait, s), "peer_reduce");
+    return 0;
+}
+
+int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                         const void* geom_state, const void* image_state, const void* binning_state,
+                         int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
+                         void* scratch, const EagsPeerRoute* route, void* stream) {
+    if (route && (!g || !route_ok(route, g->P) || g->cov3D_precomp))
+        return fail(EAGS_ERR_INVALID, "eags_backward_routed: bad route (or cov3D_precomp inputs)");
     if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_backward: bad view settings");
     if (!gauss_ok(view, g)) return fail(EAGS_ERR_INVALID, "eags_backward: bad Gaussian inputs");
     if (!gin || !gin->dL_dcolor || !gin->dL_ddepth || !gout)
@@ -180,7 +209,7 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
     double* pose_acc = (double*)((char*)scratch + SL.pose);
     CHECK_CUDA(cudaMemsetAsync(scratch, 0, SL.pose + 256, s), "memset(scratch)");
     CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, (unsigned*)((char*)scratch + SL.pose + 128), g_opt_tma.load(), s), "blend_bwd");
-    CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, s), "preprocess_bwd");
+    CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, route, s), "preprocess_bwd");
     return 0;
 }
 

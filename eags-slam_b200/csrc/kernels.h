@@ -82,7 +82,7 @@ int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const Ea
                      float* grad_acc, unsigned* work, int use_tma, cudaStream_t s);
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
                           GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
-                          double* pose_acc, cudaStream_t s);
+                          double* pose_acc, const EagsPeerRoute* route, cudaStream_t s);
 
 // loss.cu
 size_t image_l1_scratch_bytes(int W, int H);
@@ -105,3 +105,7 @@ size_t neighbors_workspace_bytes(long long n_ref);
 int launch_knn_mean_dist2(const float* pts, int n, float* out, void* ws, cudaStream_t s);
 int launch_radius_has_neighbor(const float* ref, int n_ref, const float* query, int n_query,
                                float radius2, uint8_t* has_neighbor, void* ws, cudaStream_t s);
+
+// collective.cu
+size_t peer_flags_bytes();
+int launch_peer_reduce(const EagsPeerRoute& r, unsigned epoch, float scale, int wait, cudaStream_t s);

@@ -321,6 +321,13 @@ struct BwdArgs {
     float* drotations;
     float* dcov3D;
     double* pose_acc;   // 15 doubles or NULL
+    // sharded mapping (collective.cu): when route_world > 0 the xyz / scale / rotation / opacity rows
+    // of Gaussian i go to route_base[i / route_chunk] (the owner's receive slot of this rank, a peer
+    // mapping) at offsets 0 / 3 stride / 6 stride / 10 stride instead of the four pointers above
+    float* route_base[EAGS_MAX_PEERS];
+    int route_world;
+    int route_chunk;
+    long long route_stride;
 };
 
 __global__ void __launch_bounds__(PRE_THREADS)
@@ -569,22 +576,27 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             for (int m = 0; m < a.M * 3; m++) dsh[m] = 0.f;
         }
         // stores (all P rows are written: the binding hands in torch.empty buffers)
-        if (b.dmeans3D) {
-            b.dmeans3D[(size_t)3 * i] = dm[0]; b.dmeans3D[(size_t)3 * i + 1] = dm[1]; b.dmeans3D[(size_t)3 * i + 2] = dm[2];
+        float *pm = b.dmeans3D, *ps = b.dscales, *pr = b.drotations, *po = b.dopacities;
+        if (b.route_world > 0) {   // reduce-scatter by peer stores
+            float* base = b.route_base[min(i / b.route_chunk, b.route_world - 1)];
+            pm = base; ps = base + 3 * b.route_stride; pr = base + 6 * b.route_stride; po = base + 10 * b.route_stride;
+        }
+        if (pm) {
+            pm[(size_t)3 * i] = dm[0]; pm[(size_t)3 * i + 1] = dm[1]; pm[(size_t)3 * i + 2] = dm[2];
         }
         if (b.dmeans2D) {
             b.dmeans2D[(size_t)3 * i] = g2x; b.dmeans2D[(size_t)3 * i + 1] = g2y; b.dmeans2D[(size_t)3 * i + 2] = 0.f;
         }
-        if (b.dopacities) b.dopacities[i] = dop;
+        if (po) po[i] = dop;
         if (b.dcolors_precomp) {
             b.dcolors_precomp[(size_t)3 * i] = dcol[0]; b.dcolors_precomp[(size_t)3 * i + 1] = dcol[1];
             b.dcolors_precomp[(size_t)3 * i + 2] = dcol[2];
         }
-        if (b.dscales) {
-            b.dscales[(size_t)3 * i] = dscale[0]; b.dscales[(size_t)3 * i + 1] = dscale[1]; b.dscales[(size_t)3 * i + 2] = dscale[2];
+        if (ps) {
+            ps[(size_t)3 * i] = dscale[0]; ps[(size_t)3 * i + 1] = dscale[1]; ps[(size_t)3 * i + 2] = dscale[2];
         }
-        if (b.drotations)
-            *reinterpret_cast<float4*>(b.drotations + (size_t)4 * i) = make_float4(drot[0], drot[1], drot[2], drot[3]);
+        if (pr)
+            *reinterpret_cast<float4*>(pr + (size_t)4 * i) = make_float4(drot[0], drot[1], drot[2], drot[3]);
         if (b.dcov3D) {
 #pragma unroll
             for (int k = 0; k < 6; k++) b.dcov3D[(size_t)6 * i + k] = dS[k];
@@ -664,15 +676,26 @@ int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs ge
 
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
                           GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
-                          double* pose_acc, cudaStream_t s) {
+                          double* pose_acc, const EagsPeerRoute* route, cudaStream_t s) {
     if (g.P <= 0) return 0;
     PreArgs a = make_args(v, g);
     BwdArgs b;
+    b.route_world = 0; b.route_chunk = 1; b.route_stride = 0;
+    for (int k = 0; k < EAGS_MAX_PEERS; k++) b.route_base[k] = nullptr;
     b.radii = radii; b.clamped = geom.clamped; b.grad_acc = (const float4*)grad_acc;
     b.dmeans3D = gout.dL_dmeans3D; b.dmeans2D = gout.dL_dmeans2D; b.dopacities = gout.dL_dopacities;
     b.dshs = gout.dL_dshs; b.dcolors_precomp = gout.dL_dcolors_precomp; b.dscales = gout.dL_dscales;
     b.drotations = gout.dL_drotations; b.dcov3D = gout.dL_dcov3D_precomp;
     b.pose_acc = gout.dL_dtau ? pose_acc : nullptr;
+    if (route) {
+        const long long stride = ((long long)g.P + 3) & ~3ll;
+        b.route_world = route->world;
+        b.route_chunk = (int)(((((long long)g.P + route->world - 1) / route->world) + 3) & ~3ll);
+        b.route_stride = stride;
+        for (int o = 0; o < route->world; o++) b.route_base[o] = route->recv[o] + (long long)route->rank * 11 * stride;
+        // non-null so that the scale / rotation chain is evaluated; the stores follow the route
+        b.dmeans3D = b.dscales = b.drotations = b.dopacities = b.route_base[route->rank];
+    }
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(a, b);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
     int n = 1;

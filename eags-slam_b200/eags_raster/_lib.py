@@ -86,6 +86,12 @@ SIGNATURES = {
                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                 C.POINTER(EagsImageGrads), C.POINTER(EagsInputGrads), C.c_void_p,
                                 C.c_void_p]),
+    "eags_peer_flags_bytes": (C.c_size_t, []),
+    "eags_backward_routed": (C.c_int, [C.POINTER(EagsView), C.POINTER(EagsGaussians), C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                       C.POINTER(EagsImageGrads), C.POINTER(EagsInputGrads), C.c_void_p,
+                                       C.c_void_p, C.c_void_p]),
+    "eags_peer_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_float, C.c_int32, C.c_void_p]),
     "eags_image_l1_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "eags_image_l1_forward": (C.c_int, [C.POINTER(EagsImageL1), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_void_p]),

@@ -1,0 +1,154 @@
+"""Gradient exchange of sharded mapping over NVLink peer memory (csrc/collective.cu).
+
+:class:`PeerGradExchange` owns the symmetric (peer-mapped) buffers of one replicated submap --
+PyTorch's symmetric-memory allocator provides the memory and the handle exchange, nothing else -- and,
+while ``route()`` is active, makes the rasterizer's backward pass
+
+1. store each Gaussian's 11 parameter-gradient floats straight into the owner rank's receive slot
+   (reduce-scatter fused into ``preprocess_bwd``), and
+2. launch ONE ``peer_reduce`` kernel (barrier, sum in rank order, ``x scale``, push to every rank,
+   barrier),
+
+so that ``loss.backward()`` returns with the *averaged* gradients of all ranks in ``p.grad`` -- views
+of the local ``reduced`` buffer, bit-identical on every rank.  The NCCL path
+(:class:`eags_raster.sharded.FusedGradBucket`) stays as the general fallback (several views per rank
+per step, or no peer access).
+
+``emulate_world=N`` builds N ranks' buffers on ONE device with the cross-rank waits disabled: the
+single-GPU parity test of the exchange (ranks run one after the other).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+
+MAX_PEERS = 8
+
+
+class EagsPeerRoute(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("P", C.c_int64),
+                ("recv", C.c_void_p * MAX_PEERS), ("reduced", C.c_void_p * MAX_PEERS),
+                ("flags", C.c_void_p * MAX_PEERS)]
+
+
+def stride_of(P: int) -> int:
+    return (int(P) + 3) & ~3
+
+
+def owner_chunk(P: int, world: int) -> int:
+    """Gaussians per owner rank (the last rank may own fewer): ceil(P / world) rounded up to 4."""
+    return (((int(P) + world - 1) // world) + 3) & ~3
+
+
+class PeerGradExchange:
+    def __init__(self, P: int, device, group=None, emulate_world: Optional[int] = None):
+        self.P = int(P)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("PeerGradExchange needs a CUDA device (no CPU fallback)")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.stride = stride_of(P)
+        self.flat = 11 * self.stride
+        self.epoch = 0
+        lib = _lib.load()
+        self.flags_bytes = int(lib.eags_peer_flags_bytes())
+        self.emulated = emulate_world is not None
+        if self.emulated:
+            self.world, self.rank = int(emulate_world), 0
+        else:
+            import torch.distributed as dist
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if not 1 <= self.world <= MAX_PEERS:
+            raise ValueError(f"PeerGradExchange supports 1..{MAX_PEERS} ranks of one node, got {self.world}")
+        recv_b, red_b = self.world * self.flat * 4, self.flat * 4
+        self._off_reduced = (recv_b + 255) & ~255
+        self._off_flags = (self._off_reduced + red_b + 255) & ~255
+        total = self._off_flags + self.flags_bytes
+        if self.emulated:
+            self._bufs = [torch.zeros(total, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
+            bases = [b.data_ptr() for b in self._bufs]
+            self._handle = None
+        else:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm_mem
+            pg = group if group is not None else dist.group.WORLD
+            with torch.cuda.device(self.device):
+                buf = symm_mem.empty(total, dtype=torch.uint8, device=self.device)
+                self._handle = symm_mem.rendezvous(buf, pg)
+            buf.zero_()
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group)          # every rank's flags are zero before anyone signals
+            self._bufs = [buf]
+            bases = [int(p) for p in self._handle.buffer_ptrs]
+            if len(bases) != self.world or bases[self.rank] != buf.data_ptr():
+                raise RuntimeError("symmetric-memory rendezvous returned unexpected peer pointers")
+        self._bases = bases
+        self._routes = [self._make_route(r) for r in (range(self.world) if self.emulated else [self.rank])]
+
+    def _make_route(self, rank: int) -> EagsPeerRoute:
+        r = EagsPeerRoute()
+        r.rank, r.world, r.P = rank, self.world, self.P
+        for p in range(self.world):
+            r.recv[p] = self._bases[p]
+            r.reduced[p] = self._bases[p] + self._off_reduced
+            r.flags[p] = self._bases[p] + self._off_flags
+        return r
+
+    # ---- views of the local result --------------------------------------------------------------
+    def _local_buf(self, rank: Optional[int] = None) -> torch.Tensor:
+        return self._bufs[rank if self.emulated else 0]
+
+    def reduced_views(self, rank: Optional[int] = None):
+        """dict(means3D (P,3), scales (P,3), rotations (P,4), opacities (P,1)): views of the result."""
+        rank = self.rank if rank is None else rank
+        flat = self._local_buf(rank)[self._off_reduced:self._off_reduced + self.flat * 4].view(torch.float32)
+        s, P = self.stride, self.P
+        return {"means3D": flat[0:3 * P].view(P, 3), "scales": flat[3 * s:3 * s + 3 * P].view(P, 3),
+                "rotations": flat[6 * s:6 * s + 4 * P].view(P, 4), "opacities": flat[10 * s:10 * s + P].view(P, 1)}
+
+    def error_flag(self, rank: Optional[int] = None) -> int:
+        """Non-zero (the epoch) if a bounded cross-rank wait expired on this rank."""
+        rank = self.rank if rank is None else rank
+        words = self._local_buf(rank)[self._off_flags:self._off_flags + self.flags_bytes].view(torch.int32)
+        return int(words[2 * MAX_PEERS + 1])
+
+    # ---- the routed backward ----------------------------------------------------------------------
+    def route(self, scale: float = 1.0, rank: Optional[int] = None, reduce: bool = True):
+        """Context manager: the next rasterizer backward scatters to the owners and (``reduce``) runs the
+        peer reduction with ``scale`` (1 / number of views).  ``rank`` selects the emulated rank."""
+        return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce)
+
+    def route_struct(self, rank: Optional[int] = None) -> EagsPeerRoute:
+        rank = self.rank if rank is None else rank
+        return self._routes[rank if self.emulated else 0]
+
+    def reduce(self, scale: float = 1.0, rank: Optional[int] = None, epoch: Optional[int] = None) -> None:
+        """Launch the peer reduction on the current stream (all ranks must call it once per step)."""
+        lib = _lib.load()
+        if epoch is None:
+            self.epoch += 1
+            epoch = self.epoch
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(lib.eags_peer_reduce(C.byref(self.route_struct(rank)), epoch & 0xffffffff, float(scale),
+                                        0 if self.emulated else 1, stream), "eags_peer_reduce")
+
+
+class _RouteCtx:
+    def __init__(self, ex: PeerGradExchange, scale: float, rank: int, reduce: bool):
+        self.ex, self.scale, self.rank, self.do_reduce = ex, scale, rank, reduce
+
+    def __enter__(self):
+        from . import rasterize
+        self.prev = rasterize._peer_route
+        rasterize._peer_route = self
+        return self
+
+    def __exit__(self, *exc):
+        from . import rasterize
+        rasterize._peer_route = self.prev
+        return False

@@ -53,6 +53,7 @@ def reserve_capacity(device, num_keys: int) -> None:
 
 
 _arena = None
+_peer_route = None   # set by eags_raster.peer.PeerGradExchange.route() (process-wide, like _arena)
 
 
 class grad_arena:
@@ -328,10 +329,28 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                               _ptr(out["shs"]), _ptr(out["colors_precomp"]), _ptr(out["scales"]),
                               _ptr(out["rotations"]), _ptr(out["cov3D_precomp"]), _ptr(out["tau"]))
         scratch = torch.empty(lib.eags_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
-        _lib.check(lib.eags_backward(C.byref(view), C.byref(g), state.radii.data_ptr(),
-                                     state.geom.data_ptr(), state.image.data_ptr(),
-                                     state.binning.data_ptr(), state.capacity, C.byref(gin),
-                                     C.byref(gout), scratch.data_ptr(), stream), "eags_backward")
+        route = _peer_route
+        if route is not None and not pose_only:
+            # sharded mapping: xyz / scale / rotation / opacity gradients are scattered to their owner
+            # ranks by preprocess_bwd and come back reduced over all ranks (eags_raster.peer)
+            ex = route.ex
+            if ex.P != P or ex.device != device or scales is None or rotations is None:
+                raise ValueError("PeerGradExchange.route(): the exchange was built for another submap "
+                                 f"(P {ex.P} on {ex.device}) or the inputs use cov3D_precomp")
+            _lib.check(lib.eags_backward_routed(C.byref(view), C.byref(g), state.radii.data_ptr(),
+                                                state.geom.data_ptr(), state.image.data_ptr(),
+                                                state.binning.data_ptr(), state.capacity, C.byref(gin),
+                                                C.byref(gout), scratch.data_ptr(),
+                                                C.byref(ex.route_struct(route.rank)), stream),
+                       "eags_backward_routed")
+            if route.do_reduce:
+                ex.reduce(route.scale, route.rank)
+            out.update(ex.reduced_views(route.rank))
+        else:
+            _lib.check(lib.eags_backward(C.byref(view), C.byref(g), state.radii.data_ptr(),
+                                         state.geom.data_ptr(), state.image.data_ptr(),
+                                         state.binning.data_ptr(), state.capacity, C.byref(gin),
+                                         C.byref(gout), scratch.data_ptr(), stream), "eags_backward")
         del keep
     return out
 

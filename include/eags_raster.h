@@ -138,6 +138,38 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
                   int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
                   void* scratch, void* stream);
 
+/* ---- Sharded mapping: gradient exchange over NVLink peer memory -------------------
+ * One process per GPU, every rank renders its own keyframe view of a replicated submap
+ * (the reference optimises one view per step on one GPU, src/entities/mapper.py:143-170; it has no
+ * collective).  Instead of "write gradients locally, then all-reduce", eags_backward_routed makes
+ * preprocess_bwd store the 11 parameter-gradient floats of Gaussian i (xyz 3, scale 3, rotation 4,
+ * opacity 1) directly into slot `rank` of the receive area of the rank that owns i
+ * (owner = i / chunk, chunk = ceil(P / world) rounded up to 4), through peer-mapped pointers;
+ * eags_peer_reduce then runs ONE kernel per rank: barrier, sum of the `world` slots in rank order
+ * (bit-identical result on every rank), x `scale`, push of the owned slice into every rank's
+ * `reduced` buffer, barrier.  All buffers are caller-owned symmetric (peer-mapped) device memory:
+ *   recv[o]    : rank o's receive area, world x 11 x stride floats, stride = (P + 3) & ~3
+ *                (slot q at q * 11 * stride; inside a slot: xyz at 0, scale at 3 stride, rotation at
+ *                6 stride, opacity at 10 stride)
+ *   reduced[p] : rank p's result, 11 x stride floats, same layout
+ *   flags[p]   : rank p's signal words, eags_peer_flags_bytes() bytes, zeroed once before first use
+ * `epoch` must increase by one per eags_peer_reduce call (start at 1), identically on all ranks.
+ * `wait` = 0 skips the cross-rank waits (single-GPU emulation of several ranks in tests). */
+#define EAGS_MAX_PEERS 8
+typedef struct EagsPeerRoute {
+    int32_t rank, world;
+    int64_t P;
+    float* recv[EAGS_MAX_PEERS];
+    float* reduced[EAGS_MAX_PEERS];
+    uint32_t* flags[EAGS_MAX_PEERS];
+} EagsPeerRoute;
+size_t eags_peer_flags_bytes(void);
+int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                         const void* geom_state, const void* image_state, const void* binning_state,
+                         int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
+                         void* scratch, const EagsPeerRoute* route, void* stream);
+int eags_peer_reduce(const EagsPeerRoute* route, uint32_t epoch, float scale, int32_t wait, void* stream);
+
 /* ---- Fused image-space losses ---------------------------------------------
  * The per-iteration losses that bracket the rasterizer in the reference: the tracking loss
  * (src/entities/tracker.py:99-128: |x - y| + eps, depth-valid mask, alpha^3 weighting, each sum

@@ -1,0 +1,94 @@
+"""Gradient exchange of sharded mapping (csrc/collective.cu, eags_raster/peer.py).
+
+Single-GPU part: `world` ranks are emulated on one device (all ranks' symmetric buffers live on it, the
+cross-rank waits are disabled, ranks run one after the other -- B200_PROFILING.md: never spin across
+ranks on one GPU): the routed backward + peer reduction must equal scale * sum over ranks of the
+plain backward's gradients (to fp32 rounding), and every rank must receive bit-identical results.
+Multi-GPU part (needs >= 2 devices): tests/peer_2gpu_check.py under torchrun."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from eags_raster import scene
+from helpers import Settings
+
+pytestmark = pytest.mark.gpu
+KEYS = ("means3D", "scales", "rotations", "opacities")
+TOL = 1e-5   # of the tensor's max |gradient|: run-to-run atomics order in blend_bwd + fp32 summation order
+
+
+def _grads(st, d, dC, dD, ex=None, rank=0, reduce=False):
+    from eags_raster import rasterize as rz
+    out = rz.rasterize_forward(st, 0, d["means3D"], d["opacities"], shs=d["shs"], scales=d["scales"],
+                               rotations=d["rotations"])
+    state = out[5]
+    args = (st, state, d["means3D"], d["opacities"], d["shs"], None, d["scales"], d["rotations"], None, dC, dD, None)
+    if ex is None:
+        return rz.rasterize_backward(*args)
+    with ex.route(rank=rank, reduce=reduce):
+        return rz.rasterize_backward(*args)
+
+
+@pytest.mark.parametrize("world,P", [(2, 4001), (3, 1000), (8, 50_000), (1, 777)])
+def test_emulated_ranks_match_summed_plain_backward(world, P):
+    from eags_raster.peer import PeerGradExchange
+    dev = torch.device("cuda")
+    sc = scene.make_scene("ragged", P=P, seed=4)
+    d = {k: v.to(dev) for k, v in sc.items()}
+    views = scene.keyframe_views("ragged", 8)
+    g = torch.Generator(device="cpu").manual_seed(1)
+    ex = PeerGradExchange(P, dev, emulate_world=world)
+    plain, sets = [], []
+    for r in range(world):
+        st = Settings(views[r], dev)
+        dC = torch.randn(3, st.image_height, st.image_width, generator=g).to(dev)
+        dD = torch.randn(1, st.image_height, st.image_width, generator=g).to(dev)
+        sets.append((st, dC, dD))
+        plain.append({k: v.clone() for k, v in _grads(st, d, dC, dD).items() if k in KEYS + ("means2D",)})
+    for r, (st, dC, dD) in enumerate(sets):
+        routed = _grads(st, d, dC, dD, ex=ex, rank=r)
+        # non-routed outputs (screen-space gradient) stay local (blend_bwd commits with float atomics, so
+        # two runs agree to rounding, not bitwise)
+        assert float((routed["means2D"] - plain[r]["means2D"]).abs().max()) <= TOL * float(plain[r]["means2D"].abs().max())
+    scale = 1.0 / world
+    for r in range(world):
+        ex.reduce(scale, rank=r, epoch=1)
+    torch.cuda.synchronize()
+    for k in KEYS:
+        want = plain[0][k].clone()
+        for r in range(1, world):
+            want = want + plain[r][k]
+        want = want * scale
+        for r in range(world):
+            got = ex.reduced_views(r)[k]
+            assert got.shape == want.shape
+            assert float((got - want).abs().max()) <= TOL * float(want.abs().max()), (k, r)
+            # what every rank receives is the SAME bits (the owner reduces once and pushes to all)
+            assert torch.equal(got, ex.reduced_views(0)[k]), (k, r)
+    assert all(ex.error_flag(r) == 0 for r in range(world))
+
+
+def test_route_rejects_other_submap():
+    from eags_raster.peer import PeerGradExchange
+    dev = torch.device("cuda")
+    sc = scene.make_scene("ragged", P=500, seed=0)
+    d = {k: v.to(dev) for k, v in sc.items()}
+    st = Settings(scene.workload_camera("ragged"), dev)
+    dC = torch.zeros(3, st.image_height, st.image_width, device=dev)
+    dD = torch.zeros(1, st.image_height, st.image_width, device=dev)
+    ex = PeerGradExchange(499, dev, emulate_world=2)
+    with pytest.raises(ValueError, match="another submap"):
+        _grads(st, d, dC, dD, ex=ex, rank=0)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (NVLink peer access)")
+def test_two_gpus_peer_exchange_equals_nccl():
+    script = os.path.join(os.path.dirname(__file__), "peer_2gpu_check.py")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", script],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "peer exchange ok" in r.stdout
