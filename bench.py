@@ -150,6 +150,24 @@ def run_ours(args):
         grad_views[k] = flat_grad[off:off + P * sizes[k]].view(P, sizes[k])
         off += P * sizes[k]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    # N > 1 gradient exchange: "peer" = reduce-scatter fused into preprocess_bwd + one peer_reduce kernel
+    # over NVLink peer memory (eags_raster.peer, csrc/collective.cu); "nccl" = backward into the fused
+    # bucket + one NCCL all-reduce (the baseline; also the fallback when peer memory is unavailable)
+    exchange, collective = None, "none"
+    if world > 1:
+        collective = args.collective
+        if collective == "peer":
+            try:
+                from eags_raster.peer import PeerGradExchange
+                exchange = PeerGradExchange(P, dev)
+            except Exception as e:   # no peer access / symmetric memory on this box: say so, use NCCL
+                collective = f"nccl (peer exchange unavailable: {type(e).__name__}: {str(e)[:120]})"
+                flag = torch.ones(1, device=dev)
+            else:
+                flag = torch.zeros(1, device=dev)
+            dist.all_reduce(flag)    # all ranks must take the same path
+            if float(flag) > 0 and exchange is not None:
+                exchange, collective = None, "nccl (peer exchange unavailable on another rank)"
 
     def step(src, read_loss=False):
         leaf = {k: src[k].detach().requires_grad_(True) for k in keys}
@@ -162,7 +180,12 @@ def run_ours(args):
             loss = lc + ld
         else:                       # the same loss from stock torch ops
             loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
-        if world > 1:
+        if exchange is not None:
+            # gradients leave preprocess_bwd through NVLink to their owner rank; p.grad comes back
+            # summed over all ranks (x 1/world), bit-identical on every replica
+            with exchange.route(scale=1.0 / world):
+                loss.backward()
+        elif world > 1:
             # the backward kernel writes the 11 floats / Gaussian straight into the fused buffer
             with rz.grad_arena(**grad_views):
                 loss.backward()
@@ -245,7 +268,7 @@ def run_ours(args):
             "config": {"workload": f"{wl}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd",
                        "views_per_step_per_gpu": 1, "loss": args.loss, "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
                        "l2": "flushed before every timed step (256 MiB write, outside the events)",
-                       "parallelism": "1 view/GPU, replica per GPU" + (", NCCL all-reduce of 11 floats/Gaussian" if world > 1 else "")},
+                       "parallelism": "1 view/GPU, replica per GPU" + (", gradient exchange of 11 floats/Gaussian: " + collective if world > 1 else "")},
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms,
                     "pipeline": "H2D of step i+1 overlaps step i (copy stream, pinned source); loss read back every step"},
@@ -452,6 +475,8 @@ def main():
     ap.add_argument("--tma", type=int, default=None)
     ap.add_argument("--loss", default="fused", choices=["torch", "fused"],
                     help="L1 colour + depth loss from torch ops, or the fused loss kernels of eags_raster.losses")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: fused peer-memory gradient exchange (default) or one NCCL all-reduce")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

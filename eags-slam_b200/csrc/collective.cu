@@ -69,13 +69,29 @@ peer_reduce_kernel(EagsPeerRoute r, unsigned epoch, float scale, int wait) {
     const int seg_k[4] = {3, 3, 4, 1};
 #pragma unroll
     for (int sgm = 0; sgm < 4; sgm++) {
+        // lo is a multiple of 4 floats (stride and chunk are), so the body moves 16-byte vectors --
+        // the pushes to the peers are 128-byte coalesced NVLink stores -- and only the cloud's last
+        // rows (P not a multiple of 4) take the scalar tail
         const long long lo = seg_off[sgm] + seg_k[sgm] * g0, hi = seg_off[sgm] + seg_k[sgm] * g1;
-        for (long long e = lo + (long long)blockIdx.x * RED_THREADS + threadIdx.x; e < hi;
-             e += (long long)gridDim.x * RED_THREADS) {
-            float acc = 0.f;
-            for (int q = 0; q < r.world; q++) acc += slots[q * flat + e];
-            acc *= scale;
-            for (int p = 0; p < r.world; p++) r.reduced[p][e] = acc;
+        const long long nvec = (hi - lo) >> 2;
+        for (long long v = (long long)blockIdx.x * RED_THREADS + threadIdx.x; v < nvec;
+             v += (long long)gridDim.x * RED_THREADS) {
+            const long long e = lo + 4 * v;
+            float4 acc = *reinterpret_cast<const float4*>(slots + e);
+            for (int q = 1; q < r.world; q++) {
+                const float4 x = *reinterpret_cast<const float4*>(slots + q * flat + e);
+                acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+            }
+            acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+            for (int p = 0; p < r.world; p++) *reinterpret_cast<float4*>(r.reduced[p] + e) = acc;
+        }
+        if (blockIdx.x == 0) {
+            for (long long e = lo + 4 * nvec + threadIdx.x; e < hi; e += RED_THREADS) {
+                float acc = slots[e];
+                for (int q = 1; q < r.world; q++) acc += slots[q * flat + e];
+                acc *= scale;
+                for (int p = 0; p < r.world; p++) r.reduced[p][e] = acc;
+            }
         }
     }
 
@@ -101,7 +117,7 @@ size_t peer_flags_bytes() { return eags_align256(sizeof(PeerFlags)); }
 
 int launch_peer_reduce(const EagsPeerRoute& r, unsigned epoch, float scale, int wait, cudaStream_t s) {
     const long long chunk = ((((long long)r.P + r.world - 1) / r.world) + 3) & ~3ll;
-    long long blocks = (11 * chunk + RED_THREADS * 4 - 1) / (RED_THREADS * 4);
+    long long blocks = (11 * chunk / 4 + RED_THREADS * 2 - 1) / (RED_THREADS * 2);   // ~2 vectors per thread
     if (blocks < 1) blocks = 1;
     if (blocks > 148 * 4) blocks = 148 * 4;
     peer_reduce_kernel<<<(int)blocks, RED_THREADS, 0, s>>>(r, epoch, scale, wait);

@@ -332,6 +332,7 @@ struct BwdArgs {
 
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
+    __shared__ __align__(16) float s_stage[7 * PRE_THREADS];   // routed stores only (collective.cu)
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
     float pose[15];
 #pragma unroll
@@ -576,30 +577,63 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             for (int m = 0; m < a.M * 3; m++) dsh[m] = 0.f;
         }
         // stores (all P rows are written: the binding hands in torch.empty buffers)
-        float *pm = b.dmeans3D, *ps = b.dscales, *pr = b.drotations, *po = b.dopacities;
-        if (b.route_world > 0) {   // reduce-scatter by peer stores
+        if (b.route_world > 0) {
+            // sharded mapping: rows go to their owner rank over NVLink.  xyz / scale / opacity are staged
+            // in shared memory and leave as 16-byte vectors below (4-byte peer stores waste the link);
+            // the rotation row already is one vector.
+            s_stage[3 * threadIdx.x] = dm[0]; s_stage[3 * threadIdx.x + 1] = dm[1]; s_stage[3 * threadIdx.x + 2] = dm[2];
+            s_stage[3 * PRE_THREADS + 3 * threadIdx.x] = dscale[0];
+            s_stage[3 * PRE_THREADS + 3 * threadIdx.x + 1] = dscale[1];
+            s_stage[3 * PRE_THREADS + 3 * threadIdx.x + 2] = dscale[2];
+            s_stage[6 * PRE_THREADS + threadIdx.x] = dop;
             float* base = b.route_base[min(i / b.route_chunk, b.route_world - 1)];
-            pm = base; ps = base + 3 * b.route_stride; pr = base + 6 * b.route_stride; po = base + 10 * b.route_stride;
-        }
-        if (pm) {
-            pm[(size_t)3 * i] = dm[0]; pm[(size_t)3 * i + 1] = dm[1]; pm[(size_t)3 * i + 2] = dm[2];
+            *reinterpret_cast<float4*>(base + 6 * b.route_stride + (size_t)4 * i) = make_float4(drot[0], drot[1], drot[2], drot[3]);
+        } else {
+            if (b.dmeans3D) {
+                b.dmeans3D[(size_t)3 * i] = dm[0]; b.dmeans3D[(size_t)3 * i + 1] = dm[1]; b.dmeans3D[(size_t)3 * i + 2] = dm[2];
+            }
+            if (b.dopacities) b.dopacities[i] = dop;
+            if (b.dscales) {
+                b.dscales[(size_t)3 * i] = dscale[0]; b.dscales[(size_t)3 * i + 1] = dscale[1]; b.dscales[(size_t)3 * i + 2] = dscale[2];
+            }
+            if (b.drotations)
+                *reinterpret_cast<float4*>(b.drotations + (size_t)4 * i) = make_float4(drot[0], drot[1], drot[2], drot[3]);
         }
         if (b.dmeans2D) {
             b.dmeans2D[(size_t)3 * i] = g2x; b.dmeans2D[(size_t)3 * i + 1] = g2y; b.dmeans2D[(size_t)3 * i + 2] = 0.f;
         }
-        if (po) po[i] = dop;
         if (b.dcolors_precomp) {
             b.dcolors_precomp[(size_t)3 * i] = dcol[0]; b.dcolors_precomp[(size_t)3 * i + 1] = dcol[1];
             b.dcolors_precomp[(size_t)3 * i + 2] = dcol[2];
         }
-        if (ps) {
-            ps[(size_t)3 * i] = dscale[0]; ps[(size_t)3 * i + 1] = dscale[1]; ps[(size_t)3 * i + 2] = dscale[2];
-        }
-        if (pr)
-            *reinterpret_cast<float4*>(pr + (size_t)4 * i) = make_float4(drot[0], drot[1], drot[2], drot[3]);
         if (b.dcov3D) {
 #pragma unroll
             for (int k = 0; k < 6; k++) b.dcov3D[(size_t)6 * i + k] = dS[k];
+        }
+    }
+    if (b.route_world > 0) {   // kernel-uniform
+        if (i >= a.P) {        // rows past the cloud pad the last vectors with zeros
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                s_stage[3 * threadIdx.x + k] = 0.f;
+                s_stage[3 * PRE_THREADS + 3 * threadIdx.x + k] = 0.f;
+            }
+            s_stage[6 * PRE_THREADS + threadIdx.x] = 0.f;
+        }
+        __syncthreads();
+        // the CTA's 256 rows are 192 + 192 + 64 vectors; owner boundaries are multiples of 4 Gaussians, so
+        // a vector never straddles two owners
+        const long long i0 = (long long)blockIdx.x * PRE_THREADS;
+        constexpr int V3 = 3 * PRE_THREADS / 4, V1 = PRE_THREADS / 4;
+        for (int t = threadIdx.x; t < 2 * V3 + V1; t += PRE_THREADS) {
+            const int seg = t < V3 ? 0 : (t < 2 * V3 ? 1 : 2);
+            const int tt = t - seg * V3, k = seg < 2 ? 3 : 1;
+            const long long gidx = i0 + (4 * tt) / k;
+            if (gidx >= a.P) continue;
+            float* base = b.route_base[min((int)(gidx / b.route_chunk), b.route_world - 1)];
+            const long long off = (seg == 0 ? 0 : (seg == 1 ? 3 : 10)) * b.route_stride + k * i0 + 4 * tt;
+            *reinterpret_cast<float4*>(base + off) =
+                *reinterpret_cast<const float4*>(&s_stage[(seg == 0 ? 0 : (seg == 1 ? 3 : 6)) * PRE_THREADS + 4 * tt]);
         }
     }
     if (b.pose_acc) {
