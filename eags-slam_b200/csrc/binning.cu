@@ -28,9 +28,9 @@ constexpr int SCAN_THREADS = 1024;
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(ImagePtrs img) {
     __shared__ unsigned s_warp[SCAN_THREADS / 32];
-    __shared__ unsigned s_carry;
+    __shared__ unsigned s_carry, s_max;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_carry = 0;
+    if (tid == 0) { s_carry = 0; s_max = 0; }
     __syncthreads();
     for (int base = 0; base < img.G; base += SCAN_THREADS) {
         const int t = base + tid;
@@ -42,6 +42,10 @@ tile_scan_kernel(ImagePtrs img) {
             if (lane >= o) incl += n;
         }
         if (lane == 31) s_warp[warp] = incl;
+        {
+            const unsigned m = __reduce_max_sync(0xffffffffu, c);
+            if (lane == 0 && m) atomicMax(&s_max, m);
+        }
         __syncthreads();
         if (warp == 0) {
             unsigned w = s_warp[lane];
@@ -69,7 +73,10 @@ tile_scan_kernel(ImagePtrs img) {
         if (tid == SCAN_THREADS - 1) s_carry = start + c;
         __syncthreads();
     }
-    if (tid == 0) img.ctrl->num_scanned = s_carry;
+    if (tid == 0) {
+        img.ctrl->num_scanned = s_carry;
+        img.ctrl->max_tile = s_max;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -246,22 +253,25 @@ __device__ __forceinline__ void pack_sorted(const unsigned long long* s, int n, 
 
 __global__ void __launch_bounds__(256)
 sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ unsorted,
-                       long long capacity, PackArgs a) {
+                       long long capacity, unsigned tile_cap, PackArgs a) {
     __shared__ unsigned long long s_keys[EAGS_SORT_SMALL_CAP];
     if (img.ctrl->num_rendered > (unsigned long long)capacity) return;
+    if (tile_cap && img.ctrl->bucket_overflow) return;
     const unsigned tile = blockIdx.x;
     const uint2 rg = img.ranges[tile];
     const int n = (int)(rg.y - rg.x);
     if (n <= 0 || n > EAGS_SORT_SMALL_CAP) return;
-    load_and_sort<256>(s_keys, unsorted + (size_t)rg.x, n);
+    // bucketed forward: the tile's keys sit in its fixed-stride bucket, not at the scanned offset
+    load_and_sort<256>(s_keys, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
     pack_sorted<256>(s_keys, n, rg.x, tile, a);
 }
 
 __global__ void __launch_bounds__(1024)
 sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, long long capacity,
-                     PackArgs a) {
+                     unsigned tile_cap, PackArgs a) {
     extern __shared__ unsigned long long s_big[];
     if (img.ctrl->num_rendered > (unsigned long long)capacity) return;
+    if (tile_cap && img.ctrl->bucket_overflow) return;
     const unsigned n_big = img.ctrl->n_big;
     for (unsigned b = blockIdx.x; b < n_big; b += gridDim.x) {
         const unsigned tile = img.big_list[b];
@@ -269,10 +279,10 @@ sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, l
         const int n = (int)(rg.y - rg.x);
         if (n <= EAGS_SORT_BIG_CAP) {
             __syncthreads();   // previous tile's pack has finished reading s_big
-            load_and_sort<1024>(s_big, unsorted + (size_t)rg.x, n);
+            load_and_sort<1024>(s_big, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
             pack_sorted<1024>(s_big, n, rg.x, tile, a);
         } else {
-            unsigned long long* g = unsorted + (size_t)rg.x;   // in place, in global memory
+            unsigned long long* g = unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x);   // in place, in global memory
             bitonic_sort_generic<1024>(g, n);
             pack_sorted<1024>(g, n, rg.x, tile, a);
         }
@@ -286,11 +296,11 @@ int launch_tile_scan(ImagePtrs img, cudaStream_t s) {
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, cudaStream_t s) {
+int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, cudaStream_t s) {
     PackArgs a;
     a.xy = geom.xy; a.conic_opacity = geom.conic_opacity; a.rgbd = geom.rgbd;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
-    sort_pack_small_kernel<<<img.G, 256, 0, s>>>(img, bin.unsorted, bin.capacity, a);
+    sort_pack_small_kernel<<<img.G, 256, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
     static const size_t big_smem = (size_t)EAGS_SORT_BIG_CAP * sizeof(unsigned long long);
     // opt in to 128 KB of dynamic shared memory (per device; cheap, idempotent)
@@ -301,6 +311,6 @@ int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, cudaStream_t
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = img.G < sms ? img.G : sms;
-    sort_pack_big_kernel<<<grid, 1024, big_smem, s>>>(img, bin.unsorted, bin.capacity, a);
+    sort_pack_big_kernel<<<grid, 1024, big_smem, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
     return cudaPeekAtLastError() == cudaSuccess ? 2 : -1;
 }

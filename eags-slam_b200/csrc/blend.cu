@@ -127,6 +127,7 @@ struct FwdArgs {
     const EagsCtrl* ctrl;
     unsigned* work;
     long long capacity;
+    unsigned tile_cap;
     const uint2* ranges;
     const float4* records;
     const float* bg;
@@ -148,6 +149,7 @@ blend_fwd_kernel(FwdArgs a) {
     __shared__ int s_unit;
 
     if (a.ctrl->num_rendered > (unsigned long long)a.capacity) return;
+    if (a.tile_cap && a.ctrl->bucket_overflow) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool count_touched = VARIANT_B && a.n_touched != nullptr;
     if (TMA && tid == 0) {
@@ -530,8 +532,9 @@ int persistent_grid(K kernel, int units) {
 }  // namespace
 
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
-                     int use_tma, cudaStream_t s) {
+                     int use_tma, unsigned tile_cap, cudaStream_t s) {
     FwdArgs a;
+    a.tile_cap = tile_cap;
     a.W = v.image_width; a.H = v.image_height; a.gx = img.gx; a.n_units = img.G * UNITS_PER_TILE;
     a.ctrl = img.ctrl; a.work = &img.ctrl->work_fwd;
     a.capacity = bin.capacity; a.ranges = img.ranges; a.records = bin.records;

@@ -113,47 +113,91 @@ int eags_kernel_times(int32_t max_spans, const char** names, float* ms) {
     return n;
 }
 
-int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,
-                      void* image_state, int32_t* radii, uint64_t* num_rendered_pinned, void* stream) {
+// Shared body of the two forward flavours.  tile_cap == 0: exact path (count -> scan -> duplicate ->
+// sort).  tile_cap > 0: bucketed path -- preprocess_fwd scatters every key into its tile's fixed-stride
+// bucket of `tile_cap` slots inside `binning_state` and there is no duplicate kernel; if a tile
+// outgrows its bucket a device flag makes every later kernel exit and the caller re-issues stage 2 on
+// the exact path (the tile scan has already produced the exact cursors).
+static int forward_geom_impl(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                             void* image_state, int32_t* radii, void* ctrl_pinned, size_t ctrl_bytes,
+                             void* binning_state, int64_t capacity, int32_t with_keys, int32_t tile_cap,
+                             void* stream) {
     if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad view settings");
     if (!gauss_ok(view, g)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad Gaussian inputs");
     if (!image_state || (g->P > 0 && (!geom_state || !radii)))
         return fail(EAGS_ERR_INVALID, "eags_forward_geom: null state buffer");
+    if (tile_cap < 0 || (tile_cap > 0 && (!binning_state || capacity < 0)))
+        return fail(EAGS_ERR_INVALID, "eags_forward_geom_bucketed: bad bucket arguments");
     cudaStream_t s = (cudaStream_t)stream;
     const int W = view->image_width, H = view->image_height;
     ImageLayout IL = image_layout(W, H);
     ImagePtrs img = image_ptrs(image_state, W, H);
     GeomPtrs geom = geom_ptrs(geom_state, g->P);
+    unsigned long long* bucket = nullptr;
+    if (tile_cap > 0) bucket = binning_ptrs(binning_state, capacity, with_keys, (int64_t)IL.G * tile_cap).unsorted;
     // ctrl + tile_count are contiguous: one memset node
     CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4 * EAGS_CTR_STRIDE, s), "memset(ctrl)");
-    CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, s), "preprocess_fwd");
+    CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, bucket, (unsigned)tile_cap, s), "preprocess_fwd");
     CHECK_LAUNCH(launch_tile_scan(img, s), "tile_scan");
-    if (num_rendered_pinned)
-        CHECK_CUDA(cudaMemcpyAsync(num_rendered_pinned, &img.ctrl->num_rendered, sizeof(uint64_t),
-                                   cudaMemcpyDeviceToHost, s),
-                   "memcpy(num_rendered)");
+    if (ctrl_pinned)
+        CHECK_CUDA(cudaMemcpyAsync(ctrl_pinned, img.ctrl, ctrl_bytes, cudaMemcpyDeviceToHost, s), "memcpy(ctrl)");
     return 0;
 }
 
-int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
-                        void* geom_state, void* image_state, void* binning_state, int64_t capacity,
-                        int32_t with_keys, const EagsImages* out, void* stream) {
+static int forward_render_impl(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                               void* geom_state, void* image_state, void* binning_state, int64_t capacity,
+                               int32_t with_keys, int32_t tile_cap, const EagsImages* out, void* stream) {
     if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_forward_render: bad view settings");
     if (!g || g->P < 0 || !image_state || !binning_state || capacity < 0 || !out || !out->color ||
-        !out->depth || !out->third || (g->P > 0 && (!geom_state || !radii)))
+        !out->depth || !out->third || (g->P > 0 && (!geom_state || !radii)) || tile_cap < 0)
         return fail(EAGS_ERR_INVALID, "eags_forward_render: null buffer");
     if (capacity >= (1ll << 32)) return fail(EAGS_ERR_INVALID, "eags_forward_render: capacity must be < 2^32");
     cudaStream_t s = (cudaStream_t)stream;
     const int W = view->image_width, H = view->image_height;
     ImagePtrs img = image_ptrs(image_state, W, H);
     GeomPtrs geom = geom_ptrs(geom_state, g->P);
-    BinningPtrs bin = binning_ptrs(binning_state, capacity, with_keys);
+    BinningPtrs bin = binning_ptrs(binning_state, capacity, with_keys, (int64_t)img.G * tile_cap);
     if (out->n_touched && g->P > 0)
         CHECK_CUDA(cudaMemsetAsync(out->n_touched, 0, (size_t)g->P * 4, s), "memset(n_touched)");
-    CHECK_LAUNCH(launch_duplicate(*view, g->P, radii, geom, img, bin, s), "duplicate");
-    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, s), "sort_pack");
-    CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), s), "blend_fwd");
+    if (tile_cap == 0) CHECK_LAUNCH(launch_duplicate(*view, g->P, radii, geom, img, bin, s), "duplicate");
+    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, (unsigned)tile_cap, s), "sort_pack");
+    CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), (unsigned)tile_cap, s), "blend_fwd");
     return 0;
+}
+
+int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                      void* image_state, int32_t* radii, uint64_t* num_rendered_pinned, void* stream) {
+    return forward_geom_impl(view, g, geom_state, image_state, radii, num_rendered_pinned, sizeof(uint64_t),
+                             nullptr, 0, 0, 0, stream);
+}
+
+int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                        void* geom_state, void* image_state, void* binning_state, int64_t capacity,
+                        int32_t with_keys, const EagsImages* out, void* stream) {
+    return forward_render_impl(view, g, radii, geom_state, image_state, binning_state, capacity, with_keys, 0,
+                               out, stream);
+}
+
+size_t eags_binning_state_bytes_bucketed(int64_t capacity, int32_t with_keys, int32_t width, int32_t height,
+                                         int32_t tile_cap) {
+    ImageLayout IL = image_layout(width, height);
+    return binning_layout(capacity, with_keys, (int64_t)IL.G * (tile_cap > 0 ? tile_cap : 0)).total;
+}
+
+int eags_forward_geom_bucketed(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                               void* image_state, int32_t* radii, EagsForwardStatus* status_pinned,
+                               void* binning_state, int64_t capacity, int32_t with_keys, int32_t tile_cap,
+                               void* stream) {
+    static_assert(sizeof(EagsForwardStatus) == sizeof(EagsCtrl), "status block mirrors the device control block");
+    return forward_geom_impl(view, g, geom_state, image_state, radii, status_pinned, sizeof(EagsCtrl),
+                             binning_state, capacity, with_keys, tile_cap, stream);
+}
+
+int eags_forward_render_bucketed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                                 void* geom_state, void* image_state, void* binning_state, int64_t capacity,
+                                 int32_t with_keys, int32_t tile_cap, const EagsImages* out, void* stream) {
+    return forward_render_impl(view, g, radii, geom_state, image_state, binning_state, capacity, with_keys,
+                               tile_cap, out, stream);
 }
 
 static bool route_ok(const EagsPeerRoute* r, int64_t P) {

@@ -56,8 +56,8 @@ static inline ImagePtrs image_ptrs(void* base, int W, int H) {
     p.gx = L.gx; p.gy = L.gy; p.G = L.G;
     return p;
 }
-static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys) {
-    BinningLayout L = binning_layout(cap, with_keys);
+static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys, int64_t bucket_slots = 0) {
+    BinningLayout L = binning_layout(cap, with_keys, bucket_slots);
     char* b = (char*)base;
     BinningPtrs p;
     p.unsorted = (unsigned long long*)(b + L.unsorted);
@@ -71,13 +71,13 @@ static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys) {
 // Every launcher returns the number of kernels it launched (>= 0) or -1 after a launch error
 // (cudaGetLastError is left set for the caller).
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
-                          int32_t* radii, cudaStream_t s);
+                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, cudaStream_t s);
 int launch_tile_scan(ImagePtrs img, cudaStream_t s);
 int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs geom, ImagePtrs img,
                      BinningPtrs bin, cudaStream_t s);
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, cudaStream_t s);
+int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, cudaStream_t s);
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
-                     int use_tma, cudaStream_t s);
+                     int use_tma, unsigned tile_cap, cudaStream_t s);
 int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
                      float* grad_acc, unsigned* work, int use_tma, cudaStream_t s);
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,

@@ -22,7 +22,8 @@
 //     n_contrib     u32[N]
 //
 //   binning state (per (tile, Gaussian) key; `cap` = capacity)
-//     unsorted      u64[cap]    (depth_bits << 32 | gaussian) bucketed by tile, unsorted
+//     unsorted      u64[max(cap, G * tile_cap)]  (depth_bits << 32 | gaussian) bucketed by tile, unsorted;
+//                               last in the buffer
 //     point_list    u32[cap]    sorted Gaussian indices (upstream: binningState.point_list)
 //     records       float4[3*cap]  the sorted, packed splat stream the blend kernels read:
 //                                  {x, y, idx, depth} {conic.xx, conic.xy, conic.yy, opacity} {r, g, b, 0}
@@ -43,7 +44,9 @@ struct EagsCtrl {
     unsigned int n_big;                // entries in big_list
     unsigned int work_sort;            // dynamic work queues of the persistent kernels
     unsigned int work_fwd;
-    unsigned int pad[9];
+    unsigned int max_tile;             // largest per-tile key count (tile_scan): sizes the next call's buckets
+    unsigned int bucket_overflow;      // bucketed forward: some tile outgrew its bucket, nothing was rendered
+    unsigned int pad[7];
 };
 static_assert(sizeof(EagsCtrl) == 64, "ctrl block is 64 bytes");
 
@@ -90,14 +93,17 @@ static inline ImageLayout image_layout(int W, int H) {
 struct BinningLayout {
     size_t unsorted, point_list, records, keys, total;
 };
-static inline BinningLayout binning_layout(int64_t cap, int with_keys) {
+// `unsorted` comes last so that the other offsets do not depend on its size: it holds either `cap`
+// keys laid out by the tile scan (exact path) or G fixed-stride buckets of `bucket_slots / G` keys
+// (bucketed path, where preprocess_fwd scatters the keys itself and there is no duplicate kernel).
+static inline BinningLayout binning_layout(int64_t cap, int with_keys, int64_t bucket_slots = 0) {
     BinningLayout L;
     if (cap < 1) cap = 1;
     size_t o = 0;
-    L.unsorted = o;   o += eags_align256((size_t)cap * 8);
     L.point_list = o; o += eags_align256((size_t)cap * 4);
     L.records = o;    o += eags_align256((size_t)cap * 48);
     L.keys = o;       o += with_keys ? eags_align256((size_t)cap * 8) : 0;
+    L.unsorted = o;   o += eags_align256((size_t)(bucket_slots > cap ? bucket_slots : cap) * 8);
     L.total = o + 256;
     return L;
 }

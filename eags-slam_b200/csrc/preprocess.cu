@@ -207,7 +207,8 @@ __device__ __forceinline__ void load_cov6(const PreArgs& a, int i, float c6[6]) 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
-                      uint32_t* __restrict__ tile_count, EagsCtrl* __restrict__ ctrl) {
+                      uint32_t* __restrict__ tile_count, EagsCtrl* __restrict__ ctrl,
+                      unsigned long long* __restrict__ bucket, unsigned tile_cap) {
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
     unsigned my_tiles = 0;
     if (i < a.P) {
@@ -263,9 +264,39 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
             geom.clamped[i] = (uint8_t)clamped;
             r_out = r;
             my_tiles = (unsigned)((x1 - x0) * (y1 - y0));
-            // per-tile key counts: no-return RED atomics spread over G addresses
-            for (int y = y0; y < y1; y++)
-                for (int x = x0; x < x1; x++) atomicAdd(&tile_count[(size_t)(y * a.gx + x) * EAGS_CTR_STRIDE], 1u);
+            if (bucket == nullptr) {
+                // exact path: per-tile key counts only (no-return RED atomics spread over G addresses);
+                // duplicate_kernel scatters the keys after the tile scan
+                for (int y = y0; y < y1; y++)
+                    for (int x = x0; x < x1; x++) atomicAdd(&tile_count[(size_t)(y * a.gx + x) * EAGS_CTR_STRIDE], 1u);
+            } else {
+                // bucketed path: the returning atomic IS the slot inside the tile's fixed-stride bucket,
+                // so the key is scattered here and there is no second pass over the Gaussians.  Four
+                // atomics are kept in flight before the dependent stores.
+                const unsigned long long key = ((unsigned long long)__float_as_uint(pv[2]) << 32) | (unsigned)i;
+                const int n = (int)my_tiles;
+                int x = x0, y = y0;
+                bool over = false;
+                for (int b = 0; b < n; b += 4) {
+                    unsigned slot[4], tile[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (b + u < n) {
+                            tile[u] = (unsigned)(y * a.gx + x);
+                            slot[u] = atomicAdd(&tile_count[(size_t)tile[u] * EAGS_CTR_STRIDE], 1u);
+                            if (++x == x1) { x = x0; y++; }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (b + u < n) {
+                            if (slot[u] < tile_cap) bucket[(size_t)tile[u] * tile_cap + slot[u]] = key;
+                            else over = true;
+                        }
+                    }
+                }
+                if (over) ctrl->bucket_overflow = 1u;   // the caller re-issues on the exact path
+            }
         } while (0);
         radii[i] = r_out;
         geom.tiles_touched[i] = my_tiles;
@@ -691,11 +722,11 @@ PreArgs make_args(const EagsView& v, const EagsGaussians& g) {
 }  // namespace
 
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
-                          int32_t* radii, cudaStream_t s) {
+                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, cudaStream_t s) {
     if (g.P <= 0) return 0;
     PreArgs a = make_args(v, g);
     preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(
-        a, geom, radii, img.tile_count, img.ctrl);
+        a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -18,6 +18,7 @@ graph capture; an overflow raises on the next call).
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 import weakref
 from typing import NamedTuple, Optional
@@ -32,6 +33,16 @@ _sync_mode = "optimistic"
 _MIN_CAPACITY = 1 << 16
 _capacity = {}            # device index -> high-water capacity (keys)
 _tls = threading.local()  # pinned K slots / pending overflow checks per thread
+_tile_cap = {}            # (device index, W, H) -> bucket slots per tile for the bucketed forward
+_bucketed = os.environ.get("EAGS_BUCKETED", "1") != "0"   # optimistic mode: scatter keys in stage 1
+_MAX_BUCKET_SLOTS = 1 << 28                               # 2 GiB of keys; beyond that use the exact path
+
+
+def set_bucketed(on: bool) -> None:
+    """Optimistic mode only: let stage 1 scatter the keys into per-tile buckets sized from the
+    previous frames' largest tile (no duplicate kernel); off = always the exact path."""
+    global _bucketed
+    _bucketed = bool(on)
 
 
 def set_sync_mode(mode: str) -> None:
@@ -53,6 +64,7 @@ def reserve_capacity(device, num_keys: int) -> None:
 
 
 _arena = None
+_capture_ctx = None  # set by eags_raster.graph.GraphedIteration while it captures
 _peer_route = None   # set by eags_raster.peer.PeerGradExchange.route() (process-wide, like _arena)
 
 
@@ -132,6 +144,14 @@ def _pinned_slot() -> torch.Tensor:
         slot = torch.zeros(1, dtype=torch.int64).pin_memory()
         _tls.slot = slot
     return slot
+
+
+def _pinned_status() -> torch.Tensor:
+    st = getattr(_tls, "status", None)
+    if st is None:
+        st = torch.zeros(8, dtype=torch.int64).pin_memory()   # EagsForwardStatus, 64 bytes
+        _tls.status = st
+    return st
 
 
 def _round_capacity(k: int) -> int:
@@ -227,6 +247,73 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
         imgs = EagsImages(color.data_ptr(), depth.data_ptr(), third.data_ptr(), _ptr(n_touched))
         idx = device.index
         mode = _sync_mode
+        capturing = P > 0 and torch.cuda.is_current_stream_capturing()
+        if capturing:
+            # CUDA-graph capture (eags_raster.graph): no event, no host wait, nothing allocated outside
+            # the graph's pool.  Capacities come from the eager warm-up steps; every replay refreshes
+            # a pinned status block the owner of the graph checks (K <= capacity, no bucket overflow).
+            cap_ctx = _capture_ctx
+            if cap_ctx is None:
+                raise RuntimeError("eags_raster: capture the rasterizer through eags_raster.graph.GraphedIteration "
+                                   "(it warms up the capacities and owns the pinned status blocks)")
+            key = (idx, W, H)
+            cap = _capacity.get(idx, 0)
+            if cap <= 0:
+                raise RuntimeError("eags_raster: run at least one eager step before capturing a CUDA graph")
+            G = ((W + 15) // 16) * ((H + 15) // 16)
+            tile_cap = _tile_cap.get(key, 0) if _bucketed else 0
+            if tile_cap * G > _MAX_BUCKET_SLOTS:
+                tile_cap = 0
+            status = cap_ctx.take_status(cap)
+            binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
+            _lib.check(lib.eags_forward_geom_bucketed(
+                C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
+                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, stream),
+                "eags_forward_geom_bucketed")
+            _lib.check(lib.eags_forward_render_bucketed(
+                C.byref(view), C.byref(g), radii.data_ptr(), geom.data_ptr(), image.data_ptr(),
+                binning.data_ptr(), cap, int(with_keys), tile_cap, C.byref(imgs), stream),
+                "eags_forward_render_bucketed")
+            del keep
+            state = RasterState(P, M, W, H, variant, cap, bool(with_keys), -1, radii, geom, image, binning)
+            return color, depth, third, radii, n_touched, state
+        if mode == "optimistic" and P > 0:
+            # one pass: stage 1 (+ key scatter into per-tile buckets once a bound is known) and stage 2 are
+            # enqueued back to back; the host waits for the stage-1 event only
+            key = (idx, W, H)
+            G = ((W + 15) // 16) * ((H + 15) // 16)
+            tile_cap = _tile_cap.get(key, 0) if _bucketed else 0
+            if tile_cap * G > _MAX_BUCKET_SLOTS:
+                tile_cap = 0
+            cap = _capacity.get(idx, 0) or _round_capacity(max(4 * P, _MIN_CAPACITY))
+            status = _pinned_status()
+            binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
+            _lib.check(lib.eags_forward_geom_bucketed(
+                C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
+                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, stream),
+                "eags_forward_geom_bucketed")
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(device))
+            _lib.check(lib.eags_forward_render_bucketed(
+                C.byref(view), C.byref(g), radii.data_ptr(), geom.data_ptr(), image.data_ptr(),
+                binning.data_ptr(), cap, int(with_keys), tile_cap, C.byref(imgs), stream),
+                "eags_forward_render_bucketed")
+            ev.synchronize()
+            K = int(status[0])
+            s32 = status.view(torch.int32)
+            max_tile, overflow = int(s32[7]), int(s32[8])
+            if K > cap or overflow:
+                # nothing was rendered (every stage-2 kernel exited): re-issue stage 2 on the exact path
+                cap = max(cap, _round_capacity(int(K * 1.25)))
+                binning = torch.empty(lib.eags_binning_state_bytes(cap, int(with_keys)), **u8)
+                _lib.check(lib.eags_forward_render(C.byref(view), C.byref(g), radii.data_ptr(),
+                                                   geom.data_ptr(), image.data_ptr(), binning.data_ptr(), cap,
+                                                   int(with_keys), C.byref(imgs), stream), "eags_forward_render")
+            _capacity[idx] = max(_capacity.get(idx, 0), _round_capacity(int(K * 1.25)))
+            _tile_cap[key] = max(_tile_cap.get(key, 0), (int(max_tile * 1.25) + 64 + 63) & ~63)
+            del keep
+            state = RasterState(P, M, W, H, variant, cap, bool(with_keys), K, radii, geom, image, binning)
+            return color, depth, third, radii, n_touched, state
         if mode == "nosync":
             _check_pending(idx)
             slot = torch.zeros(1, dtype=torch.int64).pin_memory()

@@ -131,6 +131,33 @@ int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int3
                         void* geom_state, void* image_state, void* binning_state,
                         int64_t capacity, int32_t with_keys, const EagsImages* out, void* stream);
 
+/* Bucketed forward (optional fast path; same results).  When the caller knows an upper bound
+ * `tile_cap` of the per-tile key count (e.g. 1.25 x the largest count of the previous frame --
+ * `max_tile` below), stage 1 scatters every (depth | gaussian) key straight into its tile's
+ * fixed-stride bucket inside `binning_state` (which must be eags_binning_state_bytes_bucketed(...)
+ * bytes and is needed BEFORE stage 1) and stage 2 launches no duplicate kernel.  The whole 64-byte
+ * status block is copied to pinned memory.  If `bucket_overflow` comes back non-zero (or
+ * num_rendered > capacity) nothing was rendered: re-issue stage 2 with eags_forward_render (exact
+ * path; the tile scan of stage 1 is still valid).  tile_cap == 0 degenerates to the exact path. */
+typedef struct EagsForwardStatus {
+    uint64_t num_rendered;    /* K = sum(tiles_touched)                                   */
+    uint64_t num_scanned;
+    uint32_t n_big, work_sort, work_fwd;
+    uint32_t max_tile;        /* largest per-tile key count of this view                  */
+    uint32_t bucket_overflow; /* != 0: a tile outgrew tile_cap                            */
+    uint32_t pad[7];
+} EagsForwardStatus;
+size_t eags_binning_state_bytes_bucketed(int64_t capacity, int32_t with_keys, int32_t width,
+                                         int32_t height, int32_t tile_cap);
+int eags_forward_geom_bucketed(const EagsView* view, const EagsGaussians* g, void* geom_state,
+                               void* image_state, int32_t* radii, EagsForwardStatus* status_pinned,
+                               void* binning_state, int64_t capacity, int32_t with_keys,
+                               int32_t tile_cap, void* stream);
+int eags_forward_render_bucketed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
+                                 void* geom_state, void* image_state, void* binning_state,
+                                 int64_t capacity, int32_t with_keys, int32_t tile_cap,
+                                 const EagsImages* out, void* stream);
+
 /* Backward: blend backward (warp-reduced, <= 1 vector atomic per (tile, Gaussian)) and preprocess
  * backward (+ closed-form camera-pose gradient when dL_dtau is non-NULL). */
 int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
