@@ -203,6 +203,50 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step(devt)
     barrier()
+    # launch mode "graph" (N = 1): the iteration built from the public API is captured ONCE into a CUDA
+    # graph (eags_raster.graph.GraphedIteration; static input / gradient tensors, as a tracking or mapping
+    # loop has) and replayed -- the same kernels, one launch per step instead of ~0.4 ms of Python, autograd
+    # and launch work plus one host wait.  "eager" issues every step through Python.
+    use_graph = args.launch == "graph" and world == 1
+    order = keys + ("shs",)
+    sizes_h = [devt[k].numel() for k in order]
+
+    def views_of(flat):
+        bufs, o = {}, 0
+        for k, n_ in zip(order, sizes_h):
+            bufs[k] = flat[o:o + n_].view(devt[k].shape)
+            o += n_
+        return bufs
+
+    gi, graph_launches = None, None
+    if use_graph:
+        from eags_raster.graph import GraphedIteration
+        static_flat = torch.cat([devt[k].reshape(-1) for k in order])
+        static = views_of(static_flat)
+        leaves = {k: static[k].requires_grad_(True) for k in keys}
+
+        def graph_fn():
+            for t_ in leaves.values():
+                t_.grad = None
+            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+            color, depth, alpha, radii = raster(means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"],
+                                                shs=static["shs"], colors_precomp=None, scales=leaves["scales"],
+                                                rotations=leaves["rotations"], cov3D_precomp=None)
+            if args.loss == "fused":
+                lc, ld = masked_l1_means(color, depth, gt_c, gt_d)
+                loss = lc + ld
+            else:
+                loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
+            loss.backward()
+            return loss.detach()
+
+        lc0 = _lib.launch_count()
+        gi = GraphedIteration(graph_fn, warmup=1)
+        graph_launches = (_lib.launch_count() - lc0) / 2.0     # one eager warm-up + the captured pass
+        for _ in range(3):
+            gi.replay()
+        gi.check()
+    device_step = (lambda: gi.replay()) if use_graph else (lambda: step(devt))
     l0 = _lib.launch_count()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -213,12 +257,26 @@ def run_ours(args):
     for a, b in evs:
         flush.zero_()
         a.record()
-        step(devt)
+        device_step()
         b.record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    launches = (_lib.launch_count() - l0) / args.steps
+    launches = graph_launches if use_graph else (_lib.launch_count() - l0) / args.steps
     ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    eager = None
+    if use_graph:
+        gi.check()     # no replay outgrew the captured buffers (it would not have been rendered)
+        n_e = min(args.steps, 100)
+        evs_e = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_e)]
+        for a, b in evs_e:
+            flush.zero_()
+            a.record()
+            step(devt)
+            b.record()
+        barrier()
+        ms_e = sum(a.elapsed_time(b) for a, b in evs_e) / n_e
+        eager = {"value": 1e3 / ms_e, "unit": UNIT, "ms_per_step": ms_e, "steps": n_e,
+                 "note": "the same step issued eagerly through Python every iteration (sync_mode optimistic)"}
     # ---- e2e: host (pinned) inputs, H2D of every Gaussian tensor + D2H of the loss, per step ----
     # Input pipeline: the copy of step i+1's inputs is issued on a copy stream while step i computes
     # (double buffering, as a data loader would); every step's inputs cross PCIe inside the timed
@@ -226,8 +284,6 @@ def run_ours(args):
     # All five Gaussian tensors live in ONE pinned host block and cross PCIe as one copy per step (the
     # step is PCIe-bound: 56 B/Gaussian at ~25 GB/s is longer than the kernels); the copies run two
     # steps ahead on a copy stream so the link never idles while the host reads the loss back.
-    order = keys + ("shs",)
-    sizes_h = [host[k].numel() for k in order]
     host_flat = torch.empty(sum(sizes_h), dtype=torch.float32).pin_memory()
     o = 0
     for k, n_ in zip(order, sizes_h):
@@ -240,13 +296,6 @@ def run_ours(args):
     RING = 3
     ring = [torch.empty(host_flat.numel(), dtype=torch.float32, device=dev) for _ in range(RING)]
     ring_free = [None] * RING   # event: the step that last read ring[j] has been issued and finished
-
-    def views_of(flat):
-        bufs, o = {}, 0
-        for k, n_ in zip(order, sizes_h):
-            bufs[k] = flat[o:o + n_].view(host[k].shape)
-            o += n_
-        return bufs
 
     ring_views = [views_of(f) for f in ring]
     loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -271,7 +320,11 @@ def run_ours(args):
                 q.append(prefetch((i + depth) % RING))
             cur = torch.cuda.current_stream()
             cur.wait_event(ev)
-            loss = step(ring_views[i % RING])
+            if use_graph:     # this step's inputs: ring slot -> the graph's static input block (D2D)
+                static_flat.copy_(ring[i % RING], non_blocking=True)
+                loss = gi.replay()
+            else:
+                loss = step(ring_views[i % RING])
             # the loss crosses to the host every step (4 B D2H into pinned memory); the host consumes it
             # one step later, as a training loop that logs its loss does, so the read never drains the GPU
             loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
@@ -293,6 +346,8 @@ def run_ours(args):
     e2e_loop(args.steps)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    if use_graph:
+        gi.check()
     clocks = sampler.stop() if rank == 0 else None
     # ---- max over ranks ----
     if world > 1:
@@ -309,13 +364,15 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{wl}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd",
-                       "views_per_step_per_gpu": 1, "loss": args.loss, "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
+                       "views_per_step_per_gpu": 1, "loss": args.loss,
+                       "launch": ("cuda-graph replay of the iteration captured from the public API (eags_raster.graph)"
+                                  if use_graph else "eager (every step issued through Python)"), "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
                        "l2": "flushed before every timed step (256 MiB write, outside the events)",
                        "parallelism": "1 view/GPU, replica per GPU" + (", gradient exchange of 11 floats/Gaussian: " + collective if world > 1 else "")},
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms,
                     "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
-            "gpu_launches": launches,
+            "gpu_launches": launches, "eager": eager,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks, "roofline": roof, "kernels": kern,
         }
@@ -520,6 +577,8 @@ def main():
                     help="L1 colour + depth loss from torch ops, or the fused loss kernels of eags_raster.losses")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N > 1: fused peer-memory gradient exchange (default) or one NCCL all-reduce")
+    ap.add_argument("--launch", default="graph", choices=["graph", "eager"],
+                    help="N = 1: replay the step from a CUDA graph (default) or issue it eagerly every step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
