@@ -185,9 +185,12 @@ blend_fwd_kernel(FwdArgs a) {
             }
         }
 
-        float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
+        // T carries the "done" flag in its sign: a live pixel has T >= 1e-4 > 0; termination (or a pixel
+        // outside the image) flips the sign and keeps the magnitude, so the saturation test below
+        // (T (1 - alpha) < 1e-4) also holds for finished pixels and no separate predicate is needed.
+        float T = inside ? 1.f : -1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
+        int lastj = -1;          // last contributor inside the current batch
         unsigned last = 0;
-        bool done = !inside;
         int issued = nb;
 
         for (int b = 0; b < nb; b++) {
@@ -204,7 +207,7 @@ blend_fwd_kernel(FwdArgs a) {
                 __syncthreads();
             }
             const float4* rec = s_rec[stage];
-            if (!__all_sync(FULL, done)) {
+            if (!__all_sync(FULL, T < 0.f)) {
                 // pass 1: one splat per lane -> bitmask of the splats that can touch this warp's block
                 unsigned mask[FWD_ROUNDS];
 #pragma unroll
@@ -215,6 +218,7 @@ blend_fwd_kernel(FwdArgs a) {
                     mask[r] = __ballot_sync(FULL, keep);
                 }
                 // pass 2: front-to-back over the survivors (warp-uniform loop, per-lane predicates)
+                lastj = -1;
 #pragma unroll
                 for (int r = 0; r < FWD_ROUNDS; r++) {
                     unsigned m = mask[r];
@@ -225,9 +229,9 @@ blend_fwd_kernel(FwdArgs a) {
                         const float dx = r0.x - pxf, dy = r0.y - pyf;
                         const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
                         const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
-                        if (done || power2 > 0.f || alpha < 1.0f / 255.0f) continue;
+                        if (power2 > 0.f || alpha < 1.0f / 255.0f) continue;
                         const float test_T = T * (1.f - alpha);
-                        if (test_T < 0.0001f) { done = true; continue; }
+                        if (test_T < 0.0001f) { T = -fabsf(T); continue; }
                         const float4 r2 = rec[3 * j + 2];
                         const float w = alpha * T;
                         C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
@@ -237,11 +241,12 @@ blend_fwd_kernel(FwdArgs a) {
                             if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
                         }
                         T = test_T;
-                        last = (unsigned)(base + j + 1);
+                        lastj = j;
                     }
                 }
+                if (lastj >= 0) last = (unsigned)(base + lastj + 1);
             }
-            const int ndone = __syncthreads_count(done ? 1 : 0);
+            const int ndone = __syncthreads_count(T < 0.f ? 1 : 0);
             if (VARIANT_B && count_touched) {
                 if (tid < cnt) {
                     const int v = s_touched[tid];
@@ -269,6 +274,7 @@ blend_fwd_kernel(FwdArgs a) {
         it += (unsigned)issued;
         __syncwarp();
 
+        T = fabsf(T);
         if (inside) {
             const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
             a.final_T[pix] = T;
