@@ -115,6 +115,14 @@ def make_workload(name, device, seed, view_id=0, P=None):
     return sc, cam, s
 
 
+_T0 = time.perf_counter()
+
+
+def _stamp(what):
+    if os.environ.get("EAGS_BENCH_STAMPS"):
+        print(f"[bench +{time.perf_counter() - _T0:7.2f}s] {what}", file=sys.stderr, flush=True)
+
+
 def run_ours(args):
     import torch.distributed as dist
     from eags_raster import _lib, rasterize as rz, state_array
@@ -199,6 +207,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    _stamp("setup done")
     # ---- warm-up, then device-timed steps with inputs resident in HBM ----
     for _ in range(max(args.warmup, 3)):
         step(devt)
@@ -207,7 +216,7 @@ def run_ours(args):
     # graph (eags_raster.graph.GraphedIteration; static input / gradient tensors, as a tracking or mapping
     # loop has) and replayed -- the same kernels, one launch per step instead of ~0.4 ms of Python, autograd
     # and launch work plus one host wait.  "eager" issues every step through Python.
-    use_graph = args.launch == "graph" and world == 1
+    use_graph = args.launch == "graph"
     order = keys + ("shs",)
     sizes_h = [devt[k].numel() for k in order]
 
@@ -218,7 +227,7 @@ def run_ours(args):
             o += n_
         return bufs
 
-    gi, graph_launches = None, None
+    gi, graph_launches, graph_error = None, None, None
     if use_graph:
         from eags_raster.graph import GraphedIteration
         static_flat = torch.cat([devt[k].reshape(-1) for k in order])
@@ -237,15 +246,34 @@ def run_ours(args):
                 loss = lc + ld
             else:
                 loss = (color - gt_c).abs().mean() + (depth - gt_d).abs().mean()
-            loss.backward()
+            if exchange is not None:
+                with exchange.route(scale=1.0 / world):
+                    loss.backward()
+            elif world > 1:
+                with rz.grad_arena(**grad_views):
+                    loss.backward()
+                dist.all_reduce(flat_grad)
+            else:
+                loss.backward()
             return loss.detach()
 
         lc0 = _lib.launch_count()
-        gi = GraphedIteration(graph_fn, warmup=1)
-        graph_launches = (_lib.launch_count() - lc0) / 2.0     # one eager warm-up + the captured pass
-        for _ in range(3):
-            gi.replay()
-        gi.check()
+        try:
+            gi = GraphedIteration(graph_fn, warmup=1)
+            ok = torch.ones(1, device=dev)
+        except Exception as e:       # e.g. a collective that cannot be captured on this stack
+            gi, ok = None, torch.zeros(1, device=dev)
+            graph_error = f"{type(e).__name__}: {str(e)[:160]}"
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)    # all ranks replay, or none does
+        if float(ok) < 1:
+            use_graph, gi = False, None
+        else:
+            graph_launches = (_lib.launch_count() - lc0) / 2.0     # one eager warm-up + the captured pass
+            for _ in range(3):
+                gi.replay()
+            gi.check()
+    _stamp("graph captured" if use_graph else "eager mode")
     device_step = (lambda: gi.replay()) if use_graph else (lambda: step(devt))
     l0 = _lib.launch_count()
     sampler = ClockSampler(local)
@@ -261,6 +289,7 @@ def run_ours(args):
         b.record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
+    _stamp("timed steps done")
     launches = graph_launches if use_graph else (_lib.launch_count() - l0) / args.steps
     ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
     eager = None
@@ -275,7 +304,11 @@ def run_ours(args):
             b.record()
         barrier()
         ms_e = sum(a.elapsed_time(b) for a, b in evs_e) / n_e
-        eager = {"value": 1e3 / ms_e, "unit": UNIT, "ms_per_step": ms_e, "steps": n_e,
+        if world > 1:
+            t_e = torch.tensor([ms_e], device=dev, dtype=torch.float64)
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+            ms_e = float(t_e[0])
+        eager = {"value": world * 1e3 / ms_e, "unit": UNIT, "ms_per_step": ms_e, "steps": n_e,
                  "note": "the same step issued eagerly through Python every iteration (sync_mode optimistic)"}
     # ---- e2e: host (pinned) inputs, H2D of every Gaussian tensor + D2H of the loss, per step ----
     # Input pipeline: the copy of step i+1's inputs is issued on a copy stream while step i computes
@@ -340,6 +373,7 @@ def run_ours(args):
             losses_read.append(float(pending[1]))
         assert len(losses_read) == n and all(v == v for v in losses_read)
 
+    _stamp("eager comparison done")
     e2e_loop(3)
     barrier()
     t0 = time.perf_counter()
@@ -348,6 +382,7 @@ def run_ours(args):
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     if use_graph:
         gi.check()
+    _stamp("e2e done")
     clocks = sampler.stop() if rank == 0 else None
     # ---- max over ranks ----
     if world > 1:
@@ -366,7 +401,7 @@ def run_ours(args):
             "config": {"workload": f"{wl}: {cam.W}x{cam.H}, {P} Gaussians, fwd + L1 colour/depth loss + bwd",
                        "views_per_step_per_gpu": 1, "loss": args.loss,
                        "launch": ("cuda-graph replay of the iteration captured from the public API (eags_raster.graph)"
-                                  if use_graph else "eager (every step issued through Python)"), "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
+                                  if use_graph else "eager (every step issued through Python)" + (f"; graph capture failed: {graph_error}" if graph_error else "")), "sync_mode": rz.get_sync_mode(), "tma": _lib.get_option("tma"),
                        "l2": "flushed before every timed step (256 MiB write, outside the events)",
                        "parallelism": "1 view/GPU, replica per GPU" + (", gradient exchange of 11 floats/Gaussian: " + collective if world > 1 else "")},
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
@@ -379,9 +414,12 @@ def run_ours(args):
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
         print(json.dumps(out), flush=True)
+    _stamp("json printed")
     if world > 1:
         dist.barrier()
+        _stamp("final barrier passed")
         dist.destroy_process_group()
+        _stamp("process group destroyed")
     return out
 
 

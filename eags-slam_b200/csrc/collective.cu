@@ -29,6 +29,8 @@ struct PeerFlags {                      // one per rank, in peer-mapped memory, 
     unsigned done[EAGS_MAX_PEERS];      // done[q]   = last epoch rank q finished pushing its slice
     unsigned cta_done;                  // local: CTAs of the running reduce kernel that finished
     unsigned error;                     // local: a bounded wait expired
+    unsigned epoch_done;                // local: reductions completed so far (device-side epoch counter:
+                                        // a CUDA-graph replay cannot pass a fresh epoch as an argument)
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
@@ -52,6 +54,9 @@ __device__ __forceinline__ bool wait_epoch(const unsigned* p, unsigned epoch, un
 __global__ void __launch_bounds__(RED_THREADS)
 peer_reduce_kernel(EagsPeerRoute r, unsigned epoch, float scale, int wait) {
     PeerFlags* mine = (PeerFlags*)r.flags[r.rank];
+    // epoch == 0: use the device-side counter (identical on all ranks: every rank launches the same
+    // sequence of reductions); it is advanced by the last CTA, after every CTA of this launch read it
+    if (epoch == 0) epoch = *(volatile unsigned*)&mine->epoch_done + 1u;
     // ---- barrier A: every rank's scatter (its preprocess_bwd, earlier on its stream) is complete
     if (blockIdx.x == 0 && threadIdx.x < r.world) {
         __threadfence_system();
@@ -102,6 +107,7 @@ peer_reduce_kernel(EagsPeerRoute r, unsigned epoch, float scale, int wait) {
         const unsigned ticket = atomicAdd(&mine->cta_done, 1u);
         if (ticket == gridDim.x - 1) {
             mine->cta_done = 0;
+            mine->epoch_done = epoch;
             __threadfence_system();
             for (int p = 0; p < r.world; p++) st_release_sys(&((PeerFlags*)r.flags[p])->done[r.rank], epoch);
             if (wait)

@@ -131,8 +131,7 @@ class PeerGradExchange:
         """Launch the peer reduction on the current stream (all ranks must call it once per step)."""
         lib = _lib.load()
         if epoch is None:
-            self.epoch += 1
-            epoch = self.epoch
+            epoch = 0     # device-side epoch counter (also valid inside a CUDA-graph replay)
         stream = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(lib.eags_peer_reduce(C.byref(self.route_struct(rank)), epoch & 0xffffffff, float(scale),
                                         0 if self.emulated else 1, stream), "eags_peer_reduce")

@@ -180,7 +180,8 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
  *                6 stride, opacity at 10 stride)
  *   reduced[p] : rank p's result, 11 x stride floats, same layout
  *   flags[p]   : rank p's signal words, eags_peer_flags_bytes() bytes, zeroed once before first use
- * `epoch` must increase by one per eags_peer_reduce call (start at 1), identically on all ranks.
+ * `epoch` = 0 uses a device-side counter kept in `flags` (valid inside CUDA-graph replays); a non-zero
+ * value must increase by one per eags_peer_reduce call (start at 1), identically on all ranks.
  * `wait` = 0 skips the cross-rank waits (single-GPU emulation of several ranks in tests). */
 #define EAGS_MAX_PEERS 8
 typedef struct EagsPeerRoute {
