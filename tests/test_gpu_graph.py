@@ -58,6 +58,9 @@ def test_replay_matches_eager_and_follows_inplace_updates():
 
 
 def test_outgrown_capture_is_reported():
+    from eags_raster import rasterize as rz
+    rz._capacity.clear()      # forget the high-water marks earlier tests left behind
+    rz._tile_cap.clear()
     leaf, fn = _setup(P=5_000)
     gi = GraphedIteration(fn)
     gi.replay()
