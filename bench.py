@@ -123,6 +123,25 @@ def _stamp(what):
         print(f"[bench +{time.perf_counter() - _T0:7.2f}s] {what}", file=sys.stderr, flush=True)
 
 
+def pin_to_gpu_numa_node(index):
+    """Run this process (and allocate its pinned host buffers) on the CPUs NVML reports as local to the
+    GPU: host<->device copies from the far socket run at about half the PCIe rate."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        before = os.sched_getaffinity(0)
+        cpus &= before
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus), before
+    except Exception:
+        pass
+    return None, None
+
+
 def run_ours(args):
     import torch.distributed as dist
     from eags_raster import _lib, rasterize as rz, state_array
@@ -136,6 +155,7 @@ def run_ours(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_cpus, all_cpus = pin_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
@@ -407,10 +427,12 @@ def run_ours(args):
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms,
                     "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
-            "gpu_launches": launches, "eager": eager,
+            "gpu_launches": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks, "roofline": roof, "kernels": kern,
         }
+        if all_cpus:
+            os.sched_setaffinity(0, all_cpus)     # the CPU baseline uses every host core
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
         print(json.dumps(out), flush=True)
