@@ -251,7 +251,10 @@ __device__ __forceinline__ void pack_sorted(const unsigned long long* s, int n, 
     }
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef SORT_THREADS
+#define SORT_THREADS 256
+#endif
+__global__ void __launch_bounds__(SORT_THREADS)
 sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ unsorted,
                        long long capacity, unsigned tile_cap, PackArgs a) {
     __shared__ unsigned long long s_keys[EAGS_SORT_SMALL_CAP];
@@ -262,8 +265,8 @@ sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ uns
     const int n = (int)(rg.y - rg.x);
     if (n <= 0 || n > EAGS_SORT_SMALL_CAP) return;
     // bucketed forward: the tile's keys sit in its fixed-stride bucket, not at the scanned offset
-    load_and_sort<256>(s_keys, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
-    pack_sorted<256>(s_keys, n, rg.x, tile, a);
+    load_and_sort<SORT_THREADS>(s_keys, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
+    pack_sorted<SORT_THREADS>(s_keys, n, rg.x, tile, a);
 }
 
 __global__ void __launch_bounds__(1024)
@@ -300,7 +303,7 @@ int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned til
     PackArgs a;
     a.xy = geom.xy; a.conic_opacity = geom.conic_opacity; a.rgbd = geom.rgbd;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
-    sort_pack_small_kernel<<<img.G, 256, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
+    sort_pack_small_kernel<<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
     static const size_t big_smem = (size_t)EAGS_SORT_BIG_CAP * sizeof(unsigned long long);
     // opt in to 128 KB of dynamic shared memory (per device; cheap, idempotent)

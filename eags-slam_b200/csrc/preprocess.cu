@@ -361,7 +361,10 @@ struct BwdArgs {
     long long route_stride;
 };
 
-__global__ void __launch_bounds__(PRE_THREADS)
+#ifndef PRE_BWD_MIN_CTAS
+#define PRE_BWD_MIN_CTAS 2
+#endif
+__global__ void __launch_bounds__(PRE_THREADS, PRE_BWD_MIN_CTAS)
 preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
     __shared__ __align__(16) float s_stage[7 * PRE_THREADS];   // routed stores only (collective.cu)
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
