@@ -504,9 +504,14 @@ class _Rasterize(torch.autograd.Function):
                     z(cov3D), tau, tau, None, None)
         # variant B upstream drops the gradient of the opacity image; variant A carries dL/dalpha
         g_third = g_third if st.variant == _lib.VARIANT_A else None
+        # registration (src/gsr/solver.py) optimises the pose only: no per-Gaussian gradient is written then
+        pose_only = ctx.want_tau and not any(needs[:8])
         out = rasterize_backward(ctx.settings, st, means3D, opacities, shs, colors_precomp, scales,
                                  rotations, cov3D, g_color, g_depth, g_third,
-                                 want_shs=bool(needs[2]), want_tau=ctx.want_tau)
+                                 want_shs=bool(needs[2]), want_tau=ctx.want_tau, pose_only=pose_only)
+        if pose_only:
+            tau = out["tau"]
+            return (None, None, None, None, None, None, None, None, tau[3:], tau[:3], None, None)
         tau = out["tau"]
         g_rho = tau[:3] if tau is not None else None
         g_theta = tau[3:] if tau is not None else None
