@@ -182,6 +182,19 @@ def test_variant_b_pose_gradient_through_theta_rho():
     assert screenspace.grad is not None
     vis = radii > 0
     assert int(n_touched[~vis].sum()) == 0
+    # registration style (src/gsr/solver.py): only the pose is optimised -> pose-only backward, no
+    # per-Gaussian gradient is produced; theta / rho gradients are the same
+    th2 = torch.nn.Parameter(torch.zeros(3, device=DEV))
+    rh2 = torch.nn.Parameter(torch.zeros(3, device=DEV))
+    frozen = {k: v.detach() for k, v in t.items()}
+    c2, _, d2, _, _ = GaussianRasterizer(raster_settings=s)(
+        means3D=frozen["means3D"], means2D=torch.zeros_like(frozen["means3D"]), shs=frozen["shs"], colors_precomp=None,
+        opacities=frozen["opacities"], scales=frozen["scales"], rotations=frozen["rotations"], cov3D_precomp=None,
+        theta=th2, rho=rh2)
+    (((c2 * wc)[:, okt]).sum() + ((d2 * wd)[:, okt]).sum()).backward()
+    assert rel_err(th2.grad.cpu().numpy(), theta.grad.cpu().numpy()) < 1e-5
+    assert rel_err(rh2.grad.cpu().numpy(), rho.grad.cpu().numpy()) < 1e-5
+
 
 
 def test_grad_arena_writes_into_fused_bucket():
