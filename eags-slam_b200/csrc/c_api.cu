@@ -330,6 +330,29 @@ int eags_radius_has_neighbor(const float* ref_points, int32_t n_ref, const float
     return 0;
 }
 
+size_t eags_ssim_scratch_bytes(int32_t C, int32_t H, int32_t W) {
+    return eags_align256((size_t)3 * C * H * W * sizeof(float)) + 256;   // three partial maps + the fp64 sum
+}
+
+int eags_ssim_forward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2, void* scratch,
+                      float* out_mean, void* stream) {
+    if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !scratch || !out_mean)
+        return fail(EAGS_ERR_INVALID, "eags_ssim_forward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    double* sum = (double*)((char*)scratch + eags_align256((size_t)3 * C * H * W * sizeof(float)));
+    CHECK_LAUNCH(launch_ssim_fwd(C, H, W, img1, img2, (float*)scratch, sum, out_mean, s), "ssim_fwd");
+    return 0;
+}
+
+int eags_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const float* img2,
+                       const void* scratch, const float* upstream, float* grad_img1, void* stream) {
+    if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !scratch || !upstream || !grad_img1)
+        return fail(EAGS_ERR_INVALID, "eags_ssim_backward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_ssim_bwd(C, H, W, img1, img2, (const float*)scratch, upstream, grad_img1, s), "ssim_bwd");
+    return 0;
+}
+
 int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t capacity,
                     int32_t with_keys, const void* geom_state, const void* image_state,
                     const void* binning_state, const void** ptr, int64_t* count, int32_t* elem_bytes) {

@@ -109,3 +109,9 @@ int launch_radius_has_neighbor(const float* ref, int n_ref, const float* query, 
 // collective.cu
 size_t peer_flags_bytes();
 int launch_peer_reduce(const EagsPeerRoute& r, unsigned epoch, float scale, int wait, cudaStream_t s);
+
+// ssim.cu
+int launch_ssim_fwd(int C, int H, int W, const float* img1, const float* img2, float* part_abc, double* sum,
+                    float* out, cudaStream_t s);
+int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, const float* part_abc,
+                    const float* upstream, float* grad1, cudaStream_t s);

@@ -112,3 +112,62 @@ def masked_l1_means(color: torch.Tensor, depth: torch.Tensor, gt_color: torch.Te
     """``l1_loss(color[:, mask], gt_color[:, mask]), l1_loss(depth[:, mask], gt_depth[mask])`` of reference
     mapper.py:161-165; plain means when ``mask`` is None."""
     return _ImageL1.apply(color, depth, None, gt_color, gt_depth, mask, False, False, 1, 0.0)
+
+
+class _Ssim(torch.autograd.Function):
+    """mean SSIM(img1, img2), gradient to ``img1`` (the rendered image); ``img2`` is the ground truth."""
+
+    @staticmethod
+    def forward(ctx, img1, img2):
+        lib = _lib.load()
+        if not img1.is_cuda:
+            raise RuntimeError("eags_raster.losses: tensors must live on a CUDA device (there is no CPU path)")
+        if img1.shape != img2.shape or img1.dim() not in (3, 4) or (img1.dim() == 4 and img1.shape[0] != 1):
+            raise ValueError("ssim expects two (C,H,W) or (1,C,H,W) images of the same shape")
+        dev = img1.device
+        Cc, H, W = (int(v) for v in img1.shape[-3:])
+        with torch.cuda.device(dev):
+            a, b = _c(img1), _c(img2)
+            scratch = torch.empty(lib.eags_ssim_scratch_bytes(Cc, H, W), dtype=torch.uint8, device=dev)
+            out = torch.empty((), dtype=torch.float32, device=dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.eags_ssim_forward(Cc, H, W, a.data_ptr(), b.data_ptr(), scratch.data_ptr(), out.data_ptr(),
+                                             stream), "eags_ssim_forward")
+        ctx.save_for_backward(a, b, scratch)
+        ctx.dims = (Cc, H, W)
+        ctx.in_shape = img1.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, up):
+        lib = _lib.load()
+        a, b, scratch = ctx.saved_tensors
+        Cc, H, W = ctx.dims
+        dev = a.device
+        with torch.cuda.device(dev):
+            up = _c(up).reshape(())
+            grad = torch.empty(Cc, H, W, dtype=torch.float32, device=dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.eags_ssim_backward(Cc, H, W, a.data_ptr(), b.data_ptr(), scratch.data_ptr(), up.data_ptr(),
+                                              grad.data_ptr(), stream), "eags_ssim_backward")
+        return grad.view(ctx.in_shape), None
+
+
+def ssim(img1: torch.Tensor, img2: torch.Tensor, window_size: int = 11, size_average: bool = True) -> torch.Tensor:
+    """``ssim(img1, img2)`` of reference src/entities/losses.py:65-85 (same signature).  The fused kernels
+    implement what the reference calls: the 11x11 window with ``size_average=True``; gradient flows to
+    ``img1``."""
+    if window_size != 11 or not size_average:
+        raise NotImplementedError("the fused SSIM implements window_size=11, size_average=True (mapper.py:163)")
+    if img2.requires_grad:
+        raise NotImplementedError("the fused SSIM differentiates with respect to img1 only (img2 is the ground truth)")
+    return _Ssim.apply(img1, img2)
+
+
+def mapping_color_loss(image: torch.Tensor, gt_image: torch.Tensor, mask: Optional[torch.Tensor],
+                       lambda_dssim: float) -> torch.Tensor:
+    """``(1 - lambda) * l1_loss(image[:, mask], gt[:, mask]) + lambda * (1 - ssim(image, gt))`` of reference
+    mapper.py:162-163, from the fused L1 and SSIM kernels."""
+    depth_dummy = image[:1]
+    l1, _ = _ImageL1.apply(image, depth_dummy, None, gt_image, depth_dummy.detach(), mask, False, True, 1, 0.0)
+    return (1.0 - lambda_dssim) * l1 + lambda_dssim * (1.0 - ssim(image, gt_image))

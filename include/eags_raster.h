@@ -227,6 +227,17 @@ int eags_image_l1_backward(int32_t width, int32_t height, const float* sums4, co
                            const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
                            void* stream);
 
+/* Fused SSIM (11x11 Gaussian window, sigma 1.5, zero padding, mean over C*H*W) -- the `ssim(img1, img2)`
+ * of src/entities/losses.py:65-113 as used by the mapping colour loss (src/entities/mapper.py:162-163).
+ * Forward writes the mean SSIM to out_mean (device float) and keeps three per-pixel partial maps in
+ * `scratch` (eags_ssim_scratch_bytes, caller-owned, must survive until the backward);
+ * backward writes d(mean ssim)/d img1 x upstream[0] (device scalar, no host sync) to grad_img1 (C,H,W). */
+size_t eags_ssim_scratch_bytes(int32_t C, int32_t height, int32_t width);
+int eags_ssim_forward(int32_t C, int32_t height, int32_t width, const float* img1, const float* img2,
+                      void* scratch, float* out_mean, void* stream);
+int eags_ssim_backward(int32_t C, int32_t height, int32_t width, const float* img1, const float* img2,
+                       const void* scratch, const float* upstream, float* grad_img1, void* stream);
+
 /* ---- Tracking fast path ----------------------------------------
  * Replaces the P-sized pose transform + its autograd of src/entities/tracker.py:85-97 by folding the
  * optimisable relative pose (quaternion q wxyz, un-normalised; translation t) into the view matrices:
