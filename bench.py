@@ -537,12 +537,13 @@ def kernel_rooflines(wl, settings, devt, gt_c, gt_d, peaks, rz, state_array, rep
         if "achieved" in row:
             row["frac"] = row["achieved"] / row["peak"]
         row["traffic"] = ncu_traffic(wl, name)
+        row["ncu"] = ncu_traffic(wl + "_ncu", name)   # issue-slot / pipe utilisation of the committed ncu capture
         table[name] = row
     top = max(table, key=lambda k: table[k]["ms"])
     t = table[top]
     roof = {
         "kernel": top, "bound": t["bound"], "achieved": t.get("achieved"), "peak": t.get("peak"),
-        "unit": t.get("unit"), "frac": t.get("frac"), "traffic": t["traffic"], "ms": t["ms"],
+        "unit": t.get("unit"), "frac": t.get("frac"), "traffic": t["traffic"], "ms": t["ms"], "ncu": t.get("ncu"),
         "peak_source": (f"fp32: 148 SM x 128 lanes x 2 x {peaks['sm_max_mhz']:.0f} MHz; hbm: {peaks['hbm_gbs']:.0f} GB/s "
                         f"(MEASURED_PEAKS.json, {peaks['src']})"),
         "note": "blending is FP32-pipe / issue-slot bound (no tensor-core work on this path); "
