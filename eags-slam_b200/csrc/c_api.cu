@@ -353,6 +353,15 @@ int eags_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const
     return 0;
 }
 
+int eags_isotropic_loss(int32_t P, const float* scaling, float* raw_grad, void* sum_scratch8, float* out_mean,
+                        void* stream) {
+    if (P <= 0 || !scaling || !raw_grad || !sum_scratch8 || !out_mean)
+        return fail(EAGS_ERR_INVALID, "eags_isotropic_loss: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_isotropic(P, scaling, raw_grad, (double*)sum_scratch8, out_mean, s), "isotropic_loss");
+    return 0;
+}
+
 int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t capacity,
                     int32_t with_keys, const void* geom_state, const void* image_state,
                     const void* binning_state, const void** ptr, int64_t* count, int32_t* elem_bytes) {

@@ -115,3 +115,4 @@ int launch_ssim_fwd(int C, int H, int W, const float* img1, const float* img2, f
                     float* out, cudaStream_t s);
 int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, const float* part_abc,
                     const float* upstream, float* grad1, cudaStream_t s);
+int launch_isotropic(int P, const float* scaling, float* grad, double* sum, float* out, cudaStream_t s);

@@ -168,3 +168,43 @@ int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, co
     image_l1_scale_kernel<<<loss_grid(N), LOSS_THREADS, 0, s>>>(N, sums, up_c, up_d, g_color, g_depth, g_alpha);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
+
+// ---- isotropic regulariser of the mapping loss (reference src/entities/losses.py:115-126) -------------
+//   loss = mean_{i,j} | s_ij - mean_j s_ij |   over scaling (P,3);  one pass: value (fp64 accumulator)
+//   and the raw gradient  d(sum)/ds_ij = sign(d_ij) - (1/3) sum_k sign(d_ik)   (sign(0) = 0 as torch.abs)
+namespace {
+__global__ void __launch_bounds__(256)
+isotropic_kernel(int P, const float* __restrict__ s, float* __restrict__ grad, double* __restrict__ sum) {
+    __shared__ double s_red[8];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    double local = 0.0;
+    if (i < P) {
+        const float a = s[(size_t)3 * i], b = s[(size_t)3 * i + 1], c = s[(size_t)3 * i + 2];
+        const float m = (a + b + c) / 3.0f;
+        const float d0 = a - m * 1.0f, d1 = b - m * 1.0f, d2 = c - m * 1.0f;
+        local = (double)(fabsf(d0) + fabsf(d1) + fabsf(d2));
+        const float g0 = (d0 > 0.f) - (d0 < 0.f), g1 = (d1 > 0.f) - (d1 < 0.f), g2 = (d2 > 0.f) - (d2 < 0.f);
+        const float gm = (g0 + g1 + g2) / 3.0f;
+        grad[(size_t)3 * i] = g0 - gm; grad[(size_t)3 * i + 1] = g1 - gm; grad[(size_t)3 * i + 2] = g2 - gm;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = local;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; k++) t += s_red[k];
+        atomicAdd(sum, t);
+    }
+}
+__global__ void isotropic_finish_kernel(const double* __restrict__ sum, float inv_count, float* __restrict__ out) {
+    out[0] = (float)(sum[0] * (double)inv_count);
+}
+}  // namespace
+
+int launch_isotropic(int P, const float* scaling, float* grad, double* sum, float* out, cudaStream_t s) {
+    if (cudaMemsetAsync(sum, 0, sizeof(double), s) != cudaSuccess) return -1;
+    isotropic_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, scaling, grad, sum);
+    isotropic_finish_kernel<<<1, 1, 0, s>>>(sum, 1.f / (3.f * (float)P), out);
+    return cudaPeekAtLastError() == cudaSuccess ? 2 : -1;
+}

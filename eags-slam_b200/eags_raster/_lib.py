@@ -109,6 +109,7 @@ SIGNATURES = {
                                     C.c_void_p]),
     "eags_ssim_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
+    "eags_isotropic_loss": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_pose_compose": (C.c_int, [C.c_void_p] * 9),
     "eags_pose_chain": (C.c_int, [C.c_void_p] * 7),
     "eags_neighbors_workspace_bytes": (C.c_size_t, [C.c_int64]),

@@ -171,3 +171,35 @@ def mapping_color_loss(image: torch.Tensor, gt_image: torch.Tensor, mask: Option
     depth_dummy = image[:1]
     l1, _ = _ImageL1.apply(image, depth_dummy, None, gt_image, depth_dummy.detach(), mask, False, True, 1, 0.0)
     return (1.0 - lambda_dssim) * l1 + lambda_dssim * (1.0 - ssim(image, gt_image))
+
+
+class _Isotropic(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, scaling):
+        lib = _lib.load()
+        if not scaling.is_cuda:
+            raise RuntimeError("eags_raster.losses: tensors must live on a CUDA device (there is no CPU path)")
+        if scaling.dim() != 2 or scaling.shape[1] != 3 or scaling.shape[0] == 0:
+            raise ValueError("isotropic_loss expects a non-empty (P, 3) scaling tensor")
+        dev = scaling.device
+        with torch.cuda.device(dev):
+            s = _c(scaling)
+            P = int(s.shape[0])
+            grad = torch.empty_like(s)
+            acc = torch.empty(1, dtype=torch.float64, device=dev)
+            out = torch.empty((), dtype=torch.float32, device=dev)
+            _lib.check(lib.eags_isotropic_loss(P, s.data_ptr(), grad.data_ptr(), acc.data_ptr(), out.data_ptr(),
+                                               torch.cuda.current_stream(dev).cuda_stream), "eags_isotropic_loss")
+        ctx.save_for_backward(grad)
+        ctx.inv = 1.0 / (3.0 * P)
+        return out
+
+    @staticmethod
+    def backward(ctx, up):
+        (grad,) = ctx.saved_tensors
+        return grad * (up * ctx.inv)
+
+
+def isotropic_loss(scaling: torch.Tensor) -> torch.Tensor:
+    """``isotropic_loss(scaling)`` of reference src/entities/losses.py:115-126 (mapper.py:166), one kernel."""
+    return _Isotropic.apply(scaling)

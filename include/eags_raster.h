@@ -238,6 +238,12 @@ int eags_ssim_forward(int32_t C, int32_t height, int32_t width, const float* img
 int eags_ssim_backward(int32_t C, int32_t height, int32_t width, const float* img1, const float* img2,
                        const void* scratch, const float* upstream, float* grad_img1, void* stream);
 
+/* Isotropic regulariser of the mapping loss (src/entities/losses.py:115-126, mapper.py:166):
+ * out_mean = mean |s_ij - mean_j s_ij| over scaling (P,3); raw_grad (P,3) = d(sum)/d scaling (the caller
+ * scales it by upstream / (3 P)); sum_scratch8: 8 bytes of device scratch (fp64 accumulator). */
+int eags_isotropic_loss(int32_t P, const float* scaling, float* raw_grad, void* sum_scratch8,
+                        float* out_mean, void* stream);
+
 /* ---- Tracking fast path ----------------------------------------
  * Replaces the P-sized pose transform + its autograd of src/entities/tracker.py:85-97 by folding the
  * optimisable relative pose (quaternion q wxyz, un-normalised; translation t) into the view matrices:

@@ -30,3 +30,16 @@ for name, (C, H, W), seed in [("ragged", (3, 37, 53), 0), ("square", (3, 64, 64)
     out[f"{name}_maploss_grad"] = img2.grad.numpy().copy()
 np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ssim_reference.npz"), **out)
 print("wrote", len(out), "arrays")
+
+# isotropic regulariser (src/entities/losses.py:115-126), value and gradient for a 2x upstream gradient
+from src.entities.losses import isotropic_loss  # noqa: E402
+
+g = torch.Generator().manual_seed(9)
+s = torch.exp(torch.randn(5001, 3, generator=g) * 0.7 - 3).requires_grad_(True)
+with torch.no_grad():
+    s[:50] = s[:50, :1]          # exactly isotropic rows: |0| has zero gradient
+v = isotropic_loss(s)
+(2.0 * v).backward()
+np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "isotropic_reference.npz"),
+                    scaling=s.detach().numpy(), loss=np.float32(v.item()), grad=s.grad.numpy())
+print("wrote isotropic_reference.npz")

@@ -59,3 +59,16 @@ def test_fused_ssim_argument_errors():
         ssim(a, a[:, :8])
     with pytest.raises(RuntimeError, match="CUDA"):
         ssim(a.cpu(), a.cpu())
+
+
+def test_fused_isotropic_loss_matches_reference_golden():
+    """src/entities/losses.py:115-126 through the reference's own code (tests/golden/isotropic_reference.npz)."""
+    from eags_raster.losses import isotropic_loss
+    R = np.load(os.path.join(os.path.dirname(__file__), "golden", "isotropic_reference.npz"))
+    s = torch.from_numpy(R["scaling"]).cuda().requires_grad_(True)
+    v = isotropic_loss(s)
+    assert abs(float(v) - float(R["loss"])) <= 2e-6 * float(R["loss"])
+    (2.0 * v).backward()
+    assert np.abs(s.grad.cpu().numpy() - R["grad"]).max() <= 1e-6 * np.abs(R["grad"]).max()
+    with pytest.raises(ValueError):
+        isotropic_loss(torch.zeros(0, 3, device="cuda"))
