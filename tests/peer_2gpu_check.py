@@ -63,7 +63,47 @@ for it in range(3):          # several epochs: flags are never reset
         dist.broadcast(c, src=0)
         assert torch.equal(c, a[k]), (it, k, "replicas differ")
 assert ex.error_flag() == 0
+
+# the same step replayed from a CUDA graph: the barrier epochs live in device memory, so every replay
+# synchronises with its peers like an eager call; parameters change in place between replays
+from eags_raster.graph import GraphedIteration  # noqa: E402
+
+static = {k: d[k].clone().requires_grad_(True) for k in keys}
+
+
+def graph_fn():
+    for t in static.values():
+        t.grad = None
+    m2d = torch.zeros_like(static["means3D"], requires_grad=True)
+    color, depth, alpha, radii = raster(means3D=static["means3D"], means2D=m2d, opacities=static["opacities"],
+                                        shs=d["shs"], colors_precomp=None, scales=static["scales"],
+                                        rotations=static["rotations"], cov3D_precomp=None)
+    loss = (color - d["gt_color"]).abs().mean() + (depth - d["gt_depth"]).abs().mean()
+    with ex.route(scale=1.0 / world):
+        loss.backward()
+    return {k: static[k].grad for k in keys}
+
+
+gi = GraphedIteration(graph_fn, warmup=1)
+for it in range(4):
+    with torch.no_grad():
+        static["means3D"].add_(1e-3)         # identical update on every rank
+    g = gi.replay()
+    gi.check()
+    d_backup = {k: d[k] for k in keys}
+    for k in keys:
+        d[k] = static[k].detach()
+    b = step(False)                           # eager NCCL reference on the updated parameters
+    for k in keys:
+        d[k] = d_backup[k]
+    for k in keys:
+        err, ref = float((g[k] - b[k]).abs().max()), float(b[k].abs().max())
+        assert err <= 1e-5 * ref + 1e-12, ("graph", it, k, err, ref)
+        c = g[k].clone()
+        dist.broadcast(c, src=0)
+        assert torch.equal(c, g[k]), ("graph", it, k, "replicas differ")
+assert ex.error_flag() == 0
 dist.barrier()
 if rank == 0:
-    print(f"peer exchange ok: world {world}, P {P}, 3 steps, max rel diff vs NCCL <= 1e-6, replicas bit-identical")
+    print(f"peer exchange ok: world {world}, P {P}, 3 eager steps + 4 graph replays, max rel diff vs NCCL <= 1e-5, replicas bit-identical")
 dist.destroy_process_group()
