@@ -3,6 +3,7 @@
               our rasterizer, torch losses
   fused-loss: same, with eags_raster.losses.tracking_losses
   fast-path : eags_raster.tracking.render_relative + tracking_losses (no P-sized torch op at all)
+  fast-path+graph: the same iteration incl. the Adam step, captured once and replayed (eags_raster.graph)
 usage: python profiles/bench_tracking.py [--iters 100]"""
 import argparse
 import os
@@ -42,11 +43,16 @@ def torch_losses(color, depth, alpha):
 def make_step(kind):
     cr = torch.tensor([1.0, 0.004, -0.003, 0.002], device=dev, requires_grad=True)
     ct = torch.tensor([0.01, -0.005, 0.008], device=dev, requires_grad=True)
-    opt = torch.optim.Adam([cr, ct], lr=1e-4)
+    graph = kind == "fast-path+graph"
+    opt = torch.optim.Adam([cr, ct], lr=1e-4, capturable=graph)
 
     def step():
-        opt.zero_grad(set_to_none=True)
-        if kind == "fast-path":
+        if graph:
+            if cr.grad is not None:
+                opt.zero_grad(set_to_none=False)
+        else:
+            opt.zero_grad(set_to_none=True)
+        if kind.startswith("fast-path"):
             color, depth, alpha, _ = render_relative(s, base["means3D"], base["opacities"], base["shs"],
                                                      base["scales"], base["rotations"], cr, ct)
         else:
@@ -64,10 +70,14 @@ def make_step(kind):
     return step
 
 
-for kind in ("ref-style", "fused-loss", "fast-path"):
+for kind in ("ref-style", "fused-loss", "fast-path", "fast-path+graph"):
     step = make_step(kind)
     for _ in range(10):
         step()
+    if kind.endswith("+graph"):       # the whole tracking iteration (incl. Adam) replayed from a CUDA graph
+        from eags_raster.graph import GraphedIteration
+        gi = GraphedIteration(step, warmup=1)
+        step = gi.replay
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -76,4 +86,6 @@ for kind in ("ref-style", "fused-loss", "fast-path"):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / a.iters
-    print(f"{kind:10s}: {ms:.4f} ms / tracking iteration  ({1e3 / ms:.0f} it/s)")
+    if kind.endswith("+graph"):
+        gi.check()
+    print(f"{kind:16s}: {ms:.4f} ms / tracking iteration  ({1e3 / ms:.0f} it/s)")
