@@ -36,7 +36,12 @@ class _CaptureCtx:
 
 class GraphedIteration:
     """``fn()`` must read its inputs from, and leave its results in, tensors that persist between
-    calls (parameters updated in place, ``.grad`` tensors, a loss tensor it returns)."""
+    calls (parameters updated in place, ``.grad`` tensors, a loss tensor it returns).  Parameters whose
+    ``.grad`` is reset to ``None`` inside ``fn`` should be fresh leaves (first used by the warm-up run
+    here): autograd ties a leaf's gradient accumulation to the stream of its first use, and a leaf that
+    already accumulated on the legacy default stream cannot do so inside a capture ("legacy stream depends
+    on a capturing stream").  Keeping the ``.grad`` tensors (``zero_grad(set_to_none=False)``) works for
+    any leaf."""
 
     def __init__(self, fn: Callable[[], object], warmup: int = 3, max_renders: int = 16, device=None):
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
