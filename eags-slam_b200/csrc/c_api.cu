@@ -205,6 +205,9 @@ static bool route_ok(const EagsPeerRoute* r, int64_t P) {
         return false;
     for (int k = 0; k < r->world; k++)
         if (!r->recv[k] || !r->reduced[k] || !r->flags[k]) return false;
+    const int n_acc = (r->accum[0] != nullptr) + (r->accum[1] != nullptr) + (r->accum[2] != nullptr) + (r->accum[3] != nullptr);
+    if (n_acc != 0 && n_acc != 4) return false;                         // all four or none
+    if (n_acc && (reinterpret_cast<uintptr_t>(r->accum[2]) & 15)) return false;   // rotation rows are read as float4
     return true;
 }
 

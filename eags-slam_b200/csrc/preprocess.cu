@@ -359,6 +359,9 @@ struct BwdArgs {
     int route_world;
     int route_chunk;
     long long route_stride;
+    // optional local partial sums (xyz, scale, rotation, opacity rows of the views this rank already
+    // rendered this step) added to this pass's rows before they leave: several views per rank per step
+    const float* route_acc[4];
 };
 
 #ifndef PRE_BWD_MIN_CTAS
@@ -615,6 +618,16 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             // sharded mapping: rows go to their owner rank over NVLink.  xyz / scale / opacity are staged
             // in shared memory and leave as 16-byte vectors below (4-byte peer stores waste the link);
             // the rotation row already is one vector.
+            if (b.route_acc[0]) {   // kernel-uniform
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    dm[k] += b.route_acc[0][(size_t)3 * i + k];
+                    dscale[k] += b.route_acc[1][(size_t)3 * i + k];
+                }
+                const float4 ar = *reinterpret_cast<const float4*>(b.route_acc[2] + (size_t)4 * i);
+                drot[0] += ar.x; drot[1] += ar.y; drot[2] += ar.z; drot[3] += ar.w;
+                dop += b.route_acc[3][i];
+            }
             s_stage[3 * threadIdx.x] = dm[0]; s_stage[3 * threadIdx.x + 1] = dm[1]; s_stage[3 * threadIdx.x + 2] = dm[2];
             s_stage[3 * PRE_THREADS + 3 * threadIdx.x] = dscale[0];
             s_stage[3 * PRE_THREADS + 3 * threadIdx.x + 1] = dscale[1];
@@ -750,6 +763,7 @@ int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32
     BwdArgs b;
     b.route_world = 0; b.route_chunk = 1; b.route_stride = 0;
     for (int k = 0; k < EAGS_MAX_PEERS; k++) b.route_base[k] = nullptr;
+    for (int k = 0; k < 4; k++) b.route_acc[k] = nullptr;
     b.radii = radii; b.clamped = geom.clamped; b.grad_acc = (const float4*)grad_acc;
     b.dmeans3D = gout.dL_dmeans3D; b.dmeans2D = gout.dL_dmeans2D; b.dopacities = gout.dL_dopacities;
     b.dshs = gout.dL_dshs; b.dcolors_precomp = gout.dL_dcolors_precomp; b.dscales = gout.dL_dscales;
@@ -763,6 +777,8 @@ int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32
         for (int o = 0; o < route->world; o++) b.route_base[o] = route->recv[o] + (long long)route->rank * 11 * stride;
         // non-null so that the scale / rotation chain is evaluated; the stores follow the route
         b.dmeans3D = b.dscales = b.drotations = b.dopacities = b.route_base[route->rank];
+        if (route->accum[0])
+            for (int k = 0; k < 4; k++) b.route_acc[k] = route->accum[k];
     }
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(a, b);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;

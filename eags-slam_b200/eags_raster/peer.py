@@ -32,7 +32,7 @@ MAX_PEERS = 8
 class EagsPeerRoute(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("P", C.c_int64),
                 ("recv", C.c_void_p * MAX_PEERS), ("reduced", C.c_void_p * MAX_PEERS),
-                ("flags", C.c_void_p * MAX_PEERS)]
+                ("flags", C.c_void_p * MAX_PEERS), ("accum", C.c_void_p * 4)]
 
 
 def stride_of(P: int) -> int:
@@ -89,6 +89,7 @@ class PeerGradExchange:
                 raise RuntimeError("symmetric-memory rendezvous returned unexpected peer pointers")
         self._bases = bases
         self._routes = [self._make_route(r) for r in (range(self.world) if self.emulated else [self.rank])]
+        self._sums = None
 
     def _make_route(self, rank: int) -> EagsPeerRoute:
         r = EagsPeerRoute()
@@ -118,14 +119,49 @@ class PeerGradExchange:
         return int(words[2 * MAX_PEERS + 1])
 
     # ---- the routed backward ----------------------------------------------------------------------
-    def route(self, scale: float = 1.0, rank: Optional[int] = None, reduce: bool = True):
+    def route(self, scale: float = 1.0, rank: Optional[int] = None, reduce: bool = True, accum=None,
+              local_views: int = 1):
         """Context manager: the next rasterizer backward scatters to the owners and (``reduce``) runs the
-        peer reduction with ``scale`` (1 / number of views).  ``rank`` selects the emulated rank."""
-        return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce)
+        peer reduction with ``scale`` (1 / number of views).  ``rank`` selects the emulated rank.
 
-    def route_struct(self, rank: Optional[int] = None) -> EagsPeerRoute:
+        ``accum`` -- dict(means3D (P,3), scales (P,3), rotations (P,4), opacities (P,1)) of contiguous
+        fp32 tensors on this device: the rank's gradient sums over the views it ALREADY rendered this
+        step (plain backward passes).  They are added to the routed rows in ``preprocess_bwd``, so with
+        several views per rank per step only the last backward goes over NVLink.
+
+        ``local_views=k`` does that bookkeeping here: the context then expects exactly k rasterizer
+        backward passes; the first k-1 run the plain backward, are summed into a buffer of this object and
+        hand NO gradient to the four routed inputs; the k-th is routed with that sum added and returns
+        the all-rank result, so the activations above the rasterizer back-propagate once per step."""
+        return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce, accum, local_views)
+
+    def _local_sums(self):
+        """(sums, scratch): two flat 11 x stride fp32 buffers for ``route(local_views > 1)``, made on first use."""
+        if self._sums is None:
+            self._sums = (torch.zeros(self.flat, dtype=torch.float32, device=self.device),
+                          torch.zeros(self.flat, dtype=torch.float32, device=self.device))
+        return self._sums
+
+    def _carve(self, flat: torch.Tensor):
+        s, P = self.stride, self.P
+        return {"means3D": flat[0:3 * P].view(P, 3), "scales": flat[3 * s:3 * s + 3 * P].view(P, 3),
+                "rotations": flat[6 * s:6 * s + 4 * P].view(P, 4), "opacities": flat[10 * s:10 * s + P].view(P, 1)}
+
+    def route_struct(self, rank: Optional[int] = None, accum=None) -> EagsPeerRoute:
         rank = self.rank if rank is None else rank
-        return self._routes[rank if self.emulated else 0]
+        base = self._routes[rank if self.emulated else 0]
+        if accum is None:
+            return base
+        r = EagsPeerRoute()
+        C.memmove(C.byref(r), C.byref(base), C.sizeof(EagsPeerRoute))
+        shapes = {"means3D": (self.P, 3), "scales": (self.P, 3), "rotations": (self.P, 4), "opacities": (self.P, 1)}
+        for k, (name, shape) in enumerate(shapes.items()):
+            t = accum.get(name)
+            if t is None or tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous() \
+                    or t.device != self.device:
+                raise ValueError(f"route(accum=...): '{name}' must be a contiguous fp32 {shape} tensor on {self.device}")
+            r.accum[k] = t.data_ptr()
+        return r
 
     def reduce(self, scale: float = 1.0, rank: Optional[int] = None, epoch: Optional[int] = None) -> None:
         """Launch the peer reduction on the current stream (all ranks must call it once per step)."""
@@ -138,8 +174,37 @@ class PeerGradExchange:
 
 
 class _RouteCtx:
-    def __init__(self, ex: PeerGradExchange, scale: float, rank: int, reduce: bool):
-        self.ex, self.scale, self.rank, self.do_reduce = ex, scale, rank, reduce
+    def __init__(self, ex: PeerGradExchange, scale: float, rank: int, reduce: bool, accum=None,
+                 local_views: int = 1):
+        if local_views < 1:
+            raise ValueError("route(local_views=...) must be >= 1")
+        if accum is not None and local_views != 1:
+            raise ValueError("route(): pass either accum= (caller-owned sums) or local_views= (summed here)")
+        self.ex, self.scale, self.rank, self.do_reduce, self.accum = ex, scale, rank, reduce, accum
+        self.local_views, self.passes = int(local_views), 0
+
+    # ---- several views per rank per step (called by rasterize_backward) ---------------------------
+    def begin_pass(self) -> bool:
+        """True if this backward pass is the rank's last of the step (the routed one)."""
+        if self.passes >= self.local_views:
+            raise RuntimeError(f"route(local_views={self.local_views}): more rasterizer backward passes than announced")
+        self.passes += 1
+        return self.passes == self.local_views
+
+    def pass_targets(self):
+        """Where a non-final pass writes its four rows: the sums themselves (first pass) or scratch."""
+        acc, tmp = self.ex._local_sums()
+        return self.ex._carve(acc if self.passes == 1 else tmp)
+
+    def end_pass(self) -> None:
+        if self.passes > 1:
+            acc, tmp = self.ex._local_sums()
+            acc.add_(tmp)
+
+    def pass_accum(self):
+        if self.accum is not None:
+            return self.accum
+        return self.ex._carve(self.ex._local_sums()[0]) if self.local_views > 1 else None
 
     def __enter__(self):
         from . import rasterize
@@ -150,4 +215,7 @@ class _RouteCtx:
     def __exit__(self, *exc):
         from . import rasterize
         rasterize._peer_route = self.prev
+        if exc[0] is None and self.passes not in (0, self.local_views):
+            raise RuntimeError(f"route(local_views={self.local_views}) saw {self.passes} backward passes: "
+                               "the step's gradients were never exchanged")
         return False

@@ -384,6 +384,18 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
         if dL_ddepth is None:
             dL_ddepth = torch.zeros(1, H, W, **f32)
         arena = _arena or {}
+        route = _peer_route if not pose_only else None
+        route_final = True
+        if route is not None:
+            ex = route.ex
+            if ex.P != P or ex.device != device or scales is None or rotations is None:
+                raise ValueError("PeerGradExchange.route(): the exchange was built for another submap "
+                                 f"(P {ex.P} on {ex.device}) or the inputs use cov3D_precomp")
+            route_final = route.begin_pass()
+            if not route_final:
+                # an earlier view of this rank's share of the step: a plain backward summed locally
+                arena = dict(arena)
+                arena.update(route.pass_targets())
 
         def buf(name, *shape):
             t = arena.get(name)
@@ -416,19 +428,15 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                               _ptr(out["shs"]), _ptr(out["colors_precomp"]), _ptr(out["scales"]),
                               _ptr(out["rotations"]), _ptr(out["cov3D_precomp"]), _ptr(out["tau"]))
         scratch = torch.empty(lib.eags_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
-        route = _peer_route
-        if route is not None and not pose_only:
-            # sharded mapping: xyz / scale / rotation / opacity gradients are scattered to their owner
-            # ranks by preprocess_bwd and come back reduced over all ranks (eags_raster.peer)
-            ex = route.ex
-            if ex.P != P or ex.device != device or scales is None or rotations is None:
-                raise ValueError("PeerGradExchange.route(): the exchange was built for another submap "
-                                 f"(P {ex.P} on {ex.device}) or the inputs use cov3D_precomp")
+        if route is not None and route_final:
+            # sharded mapping: xyz / scale / rotation / opacity gradients (plus the local sums of the
+            # rank's earlier views of this step) are scattered to their owner ranks by preprocess_bwd
+            # and come back reduced over all ranks (eags_raster.peer)
             _lib.check(lib.eags_backward_routed(C.byref(view), C.byref(g), state.radii.data_ptr(),
                                                 state.geom.data_ptr(), state.image.data_ptr(),
                                                 state.binning.data_ptr(), state.capacity, C.byref(gin),
                                                 C.byref(gout), scratch.data_ptr(),
-                                                C.byref(ex.route_struct(route.rank)), stream),
+                                                C.byref(ex.route_struct(route.rank, route.pass_accum())), stream),
                        "eags_backward_routed")
             if route.do_reduce:
                 ex.reduce(route.scale, route.rank)
@@ -438,6 +446,11 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                                          state.geom.data_ptr(), state.image.data_ptr(),
                                          state.binning.data_ptr(), state.capacity, C.byref(gin),
                                          C.byref(gout), scratch.data_ptr(), stream), "eags_backward")
+            if route is not None:
+                # the four routed inputs get no gradient from this pass: the rank's last pass of the step
+                # returns the sum over all views of all ranks (and the chain rule above them runs once)
+                route.end_pass()
+                out.update(means3D=None, scales=None, rotations=None, opacities=None)
         del keep
     return out
 
@@ -516,7 +529,7 @@ class _Rasterize(torch.autograd.Function):
         g_rho = tau[:3] if tau is not None else None
         g_theta = tau[3:] if tau is not None else None
         return (out["means3D"], out["means2D"], out["shs"], out["colors_precomp"],
-                out["opacities"].view(opacities.shape),
+                out["opacities"].view(opacities.shape) if out["opacities"] is not None else None,
                 out["scales"], out["rotations"], out["cov3D_precomp"], g_theta, g_rho, None, None)
 
 

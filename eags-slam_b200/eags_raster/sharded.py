@@ -122,15 +122,32 @@ class ShardedMapper:
     """
 
     def __init__(self, params: Sequence[torch.Tensor], optimizer: torch.optim.Optimizer,
-                 broadcast: bool = True):
+                 broadcast: bool = True, exchange=None, exchanged: Sequence[torch.Tensor] = ()):
+        """``exchange`` (:class:`eags_raster.peer.PeerGradExchange`) moves the gradients of the
+        rasterizer's xyz / scale / rotation / opacity inputs over NVLink peer memory inside the backward
+        kernel; ``exchanged`` names the parameters that receive gradient ONLY through those four inputs
+        (e.g. ``_xyz, _scaling, _rotation, _opacity``, gaussian_model.py:60-79) -- they are left out of the
+        NCCL bucket, which then carries just the rest (e.g. the SH features)."""
         self.optimizer = optimizer
-        self.bucket = FusedGradBucket(params)
+        self.exchange = exchange
+        self._exchanged_ids = {id(p) for p in exchanged}
+        if exchange is None and self._exchanged_ids:
+            raise ValueError("ShardedMapper: exchanged= needs exchange=")
+        self.rebuild(params)
         if broadcast:
-            broadcast_parameters(self.bucket.params)
+            broadcast_parameters(list(params))
 
-    def rebuild(self, params: Sequence[torch.Tensor], optimizer: Optional[torch.optim.Optimizer] = None) -> None:
-        """After add/prune changed P (gaussian_model.py:519-583) the bucket is re-carved."""
-        self.bucket = FusedGradBucket(params)
+    def rebuild(self, params: Sequence[torch.Tensor], optimizer: Optional[torch.optim.Optimizer] = None,
+                exchange=None, exchanged: Optional[Sequence[torch.Tensor]] = None) -> None:
+        """After add/prune changed P (gaussian_model.py:519-583) the bucket is re-carved (and the peer
+        exchange, sized for P, replaced)."""
+        if exchange is not None:
+            self.exchange = exchange
+        if exchanged is not None:
+            self._exchanged_ids = {id(p) for p in exchanged}
+        self._routed = [p for p in params if id(p) in self._exchanged_ids]
+        rest = [p for p in params if id(p) not in self._exchanged_ids]
+        self.bucket = FusedGradBucket(rest) if rest else None
         if optimizer is not None:
             self.optimizer = optimizer
 
@@ -139,14 +156,30 @@ class ShardedMapper:
         loss sum as a *tensor* (no host sync) and the number of views rendered locally."""
         world, rank = _world(), _rank()
         mine = [views[i] for i in shard_views(len(views), rank, world)]
-        self.bucket.attach()
+        if self.bucket is not None:
+            self.bucket.attach()
         local = None
-        for v in mine:
-            loss = loss_fn(v)
-            loss.backward()
-            local = loss.detach() if local is None else local + loss.detach()
-        self.bucket.all_reduce(divide_by=float(len(views)))
+
+        def render_all():
+            nonlocal local
+            for v in mine:
+                loss = loss_fn(v)
+                loss.backward()
+                local = loss.detach() if local is None else local + loss.detach()
+
+        if self.exchange is not None:
+            if not mine:
+                raise ValueError(f"ShardedMapper(exchange=...): rank {rank} has no view among {len(views)}; "
+                                 "every rank must render at least one per step")
+            for p in self._routed:
+                p.grad = None        # the routed pass returns the all-rank result; nothing to add it to
+            with self.exchange.route(scale=1.0 / len(views), local_views=len(mine)):
+                render_all()
+        else:
+            render_all()
+        if self.bucket is not None:
+            self.bucket.all_reduce(divide_by=float(len(views)))
         if reg_fn is not None:
-            reg_fn().backward()      # accumulates into the (already averaged) bucket, same on all ranks
+            reg_fn().backward()      # accumulates into the (already averaged) gradients, same on all ranks
         self.optimizer.step()
         return {"local_loss_sum": local, "local_views": len(mine)}

@@ -190,6 +190,11 @@ typedef struct EagsPeerRoute {
     float* recv[EAGS_MAX_PEERS];
     float* reduced[EAGS_MAX_PEERS];
     uint32_t* flags[EAGS_MAX_PEERS];
+    /* optional (all four or none): this rank's partial sums over the views it already rendered this
+     * step -- (P,3) xyz, (P,3) scale, (P,4) rotation, (P,1) opacity, local memory -- added to the routed
+     * rows of this backward pass, so a rank that renders several views per step (8-view keyframe batch
+     * on fewer than 8 GPUs) still sends each row over NVLink once */
+    const float* accum[4];
 } EagsPeerRoute;
 size_t eags_peer_flags_bytes(void);
 int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,

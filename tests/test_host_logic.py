@@ -24,8 +24,10 @@ def test_owner_chunks_partition_the_cloud_on_vector_boundaries(P, world):
 
 def test_route_struct_matches_header_layout():
     r = peer.EagsPeerRoute()
-    assert C.sizeof(r) == 4 + 4 + 8 + 3 * 8 * peer.MAX_PEERS
+    assert C.sizeof(r) == 4 + 4 + 8 + 3 * 8 * peer.MAX_PEERS + 4 * 8
     assert peer.EagsPeerRoute.recv.offset == 16 and peer.EagsPeerRoute.flags.offset == 16 + 16 * peer.MAX_PEERS
+    assert peer.EagsPeerRoute.accum.offset == 16 + 24 * peer.MAX_PEERS
+    assert all(not r.accum[k] for k in range(4))      # optional: zero unless route(accum= / local_views>1)
 
 
 def test_bucketed_binning_bytes():
