@@ -203,21 +203,71 @@ __device__ __forceinline__ void load_cov6(const PreArgs& a, int i, float c6[6]) 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Wide SH rows (M > 1: global-map refinement, evaluate_merged_map.py:67 runs sh_degree 3 -> 48 floats per
+// Gaussian).  A thread walking its own 192-byte row makes every load / store instruction of the warp
+// touch 32 different lines (32 LSU wavefronts for 128 useful bytes).  Instead each warp moves the rows it
+// needs through shared memory with fully coalesced accesses: row r of the warp sits at s_w[r * S .. ],
+// S = 3M | 1 (odd -> the per-thread walk over its own row is bank-conflict free).
+// ------------------------------------------------------------------------------------------------
+constexpr int SH_WIDE_MAX_M = 16;
+constexpr int SH_WIDE_STRIDE_MAX = (3 * SH_WIDE_MAX_M) | 1;
+constexpr size_t SH_WIDE_SMEM = (size_t)PRE_THREADS * SH_WIDE_STRIDE_MAX * sizeof(float);
+
+// rows (bit r of `rows` set) of the warp whose first Gaussian is i0w: global -> shared
+__device__ __forceinline__ void warp_rows_in(const float* __restrict__ g, long long i0w, int L, int S,
+                                             unsigned rows, float* s_w) {
+    const int lane = threadIdx.x & 31;
+    while (rows) {
+        const int r = __ffs(rows) - 1;
+        rows &= rows - 1;
+        const float* src = g + (size_t)(i0w + r) * L;
+        // asynchronous 4-byte copies (the odd row stride rules out wider ones): nothing waits until
+        // every row of the warp is in flight
+        for (int j = lane; j < L; j += 32) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_w + r * S + j);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + j) : "memory");
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+}
+
+// all `n` rows of the warp: shared (rows in `rows`) or zeros -> global
+__device__ __forceinline__ void warp_rows_out(float* __restrict__ g, long long i0w, int L, int S, int n,
+                                              unsigned rows, const float* s_w) {
+    const int lane = threadIdx.x & 31;
+    __syncwarp();
+#pragma unroll 4
+    for (int r = 0; r < n; r++) {
+        float* dst = g + (size_t)(i0w + r) * L;
+        const bool live = (rows >> r) & 1u;
+        for (int j = lane; j < L; j += 32) dst[j] = live ? s_w[r * S + j] : 0.f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // K1
 // ------------------------------------------------------------------------------------------------
+template <bool WIDE>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                       uint32_t* __restrict__ tile_count, EagsCtrl* __restrict__ ctrl,
                       unsigned long long* __restrict__ bucket, unsigned tile_cap) {
+    extern __shared__ float s_sh[];   // WIDE only: SH rows of the CTA, PRE_THREADS x S floats
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
     unsigned my_tiles = 0;
+    // phase A: geometry up to the tile rectangle; `alive` = survives every cull
+    bool alive = false;
+    float p[3] = {0.f, 0.f, 0.f};
+    float px = 0.f, py = 0.f, depth = 0.f;
+    float4 con = make_float4(0.f, 0.f, 0.f, 0.f);
+    int r = 0, x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     if (i < a.P) {
         float V[16], F[16];
         load_cam(a, V, F);
-        int r_out = 0;
         do {
-            const float p[3] = {a.means3D[(size_t)3 * i], a.means3D[(size_t)3 * i + 1],
-                                a.means3D[(size_t)3 * i + 2]};
+            p[0] = a.means3D[(size_t)3 * i]; p[1] = a.means3D[(size_t)3 * i + 1]; p[2] = a.means3D[(size_t)3 * i + 2];
             float pv[3];
             pv[0] = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
             pv[1] = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
@@ -242,12 +292,30 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
             float sq = sqrtf(fmaxf(0.1f, mid * mid - det));
             float lambda1 = mid + sq, lambda2 = mid - sq;
             float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
-            float px = ((ppx + 1.0f) * (float)a.W - 1.0f) * 0.5f;
-            float py = ((ppy + 1.0f) * (float)a.H - 1.0f) * 0.5f;
-            int r = (int)my_radius;
-            int x0, y0, x1, y1;
+            px = ((ppx + 1.0f) * (float)a.W - 1.0f) * 0.5f;
+            py = ((ppy + 1.0f) * (float)a.H - 1.0f) * 0.5f;
+            r = (int)my_radius;
             tile_rect(px, py, r, a.gx, a.gy, x0, y0, x1, y1);
             if ((x1 - x0) * (y1 - y0) == 0) break;
+            con = make_float4(cc * det_inv, -cb * det_inv, ca * det_inv, 0.f);
+            depth = pv[2];
+            alive = true;
+        } while (0);
+    }
+    // phase B (wide SH rows): the warp fetches the rows of its surviving Gaussians, coalesced
+    const float* sh_row = nullptr;
+    if constexpr (WIDE) {
+        const int L = 3 * a.M, S = L | 1;
+        float* s_w = s_sh + (size_t)(threadIdx.x >> 5) * 32 * S;
+        warp_rows_in(a.shs, (long long)i - (threadIdx.x & 31), L, S, __ballot_sync(0xffffffffu, alive), s_w);
+        sh_row = s_w + (threadIdx.x & 31) * S;
+    } else if (alive && !a.colors_precomp) {
+        sh_row = a.shs + (size_t)i * a.M * 3;
+    }
+    // phase C: colour, per-Gaussian records, tile counters / buckets
+    if (i < a.P) {
+        int r_out = 0;
+        if (alive) {
             float rgb[3];
             unsigned clamped = 0;
             if (a.colors_precomp) {
@@ -256,11 +324,12 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                 rgb[2] = a.colors_precomp[(size_t)3 * i + 2];
             } else {
                 float cp[3] = {__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)};
-                sh_to_rgb(a.degree, p, cp, a.shs + (size_t)i * a.M * 3, rgb, clamped);
+                sh_to_rgb(a.degree, p, cp, sh_row, rgb, clamped);
             }
             geom.xy[i] = make_float2(px, py);
-            geom.conic_opacity[i] = make_float4(cc * det_inv, -cb * det_inv, ca * det_inv, a.opacities[i]);
-            geom.rgbd[i] = make_float4(rgb[0], rgb[1], rgb[2], pv[2]);
+            con.w = a.opacities[i];
+            geom.conic_opacity[i] = con;
+            geom.rgbd[i] = make_float4(rgb[0], rgb[1], rgb[2], depth);
             geom.clamped[i] = (uint8_t)clamped;
             r_out = r;
             my_tiles = (unsigned)((x1 - x0) * (y1 - y0));
@@ -273,7 +342,7 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                 // bucketed path: the returning atomic IS the slot inside the tile's fixed-stride bucket,
                 // so the key is scattered here and there is no second pass over the Gaussians.  Four
                 // atomics are kept in flight before the dependent stores.
-                const unsigned long long key = ((unsigned long long)__float_as_uint(pv[2]) << 32) | (unsigned)i;
+                const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
                 const int n = (int)my_tiles;
                 int x = x0, y = y0;
                 bool over = false;
@@ -297,7 +366,7 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                 }
                 if (over) ctrl->bucket_overflow = 1u;   // the caller re-issues on the exact path
             }
-        } while (0);
+        }
         radii[i] = r_out;
         geom.tiles_touched[i] = my_tiles;
     }
@@ -367,10 +436,22 @@ struct BwdArgs {
 #ifndef PRE_BWD_MIN_CTAS
 #define PRE_BWD_MIN_CTAS 2
 #endif
+template <bool WIDE>
 __global__ void __launch_bounds__(PRE_THREADS, PRE_BWD_MIN_CTAS)
 preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
     __shared__ __align__(16) float s_stage[7 * PRE_THREADS];   // routed stores only (collective.cu)
+    extern __shared__ float s_sh[];   // WIDE only: SH rows in, dL/dSH rows out (same place)
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
+    const bool vis = i < a.P && b.radii[i] > 0;
+    float* sh_row = nullptr;
+    unsigned sh_rows = 0;
+    if constexpr (WIDE) {
+        const int L = 3 * a.M, S = L | 1;
+        float* s_w = s_sh + (size_t)(threadIdx.x >> 5) * 32 * S;
+        sh_rows = __ballot_sync(0xffffffffu, vis);
+        warp_rows_in(a.shs, (long long)i - (threadIdx.x & 31), L, S, sh_rows, s_w);
+        sh_row = s_w + (threadIdx.x & 31) * S;
+    }
     float pose[15];
 #pragma unroll
     for (int k = 0; k < 15; k++) pose[k] = 0.f;
@@ -379,7 +460,6 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
         float dS[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         float g2x = 0.f, g2y = 0.f, dop = 0.f;
         float dcol[3] = {0.f, 0.f, 0.f};
-        const bool vis = b.radii[i] > 0;
         float dmean_sh[3] = {0.f, 0.f, 0.f};
         float p[3] = {0.f, 0.f, 0.f};
         unsigned clamped = 0;
@@ -461,12 +541,14 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             // depth path: depth = row 2 of the view transform
             const float dmean_dep[3] = {V[2] * dd, V[6] * dd, V[10] * dd};
             // colour path: SH backward (incl. the view-direction term for degree > 0)
-            if (!a.colors_precomp && b.dshs) {
+            // (wide rows: dsh overwrites sh in shared memory, so within each band every sh[m] is read
+            // before dsh[m] is written; the view-direction term is also due when the SH stay frozen)
+            if (!a.colors_precomp && (WIDE || b.dshs)) {
                 float dRGB[3];
 #pragma unroll
                 for (int k = 0; k < 3; k++) dRGB[k] = (clamped >> k & 1u) ? 0.f : dcol[k];
-                float* dsh = b.dshs + (size_t)i * a.M * 3;
-                const float* sh = a.shs + (size_t)i * a.M * 3;
+                float* dsh = WIDE ? sh_row : b.dshs + (size_t)i * a.M * 3;
+                const float* sh = WIDE ? sh_row : a.shs + (size_t)i * a.M * 3;
 #pragma unroll
                 for (int k = 0; k < 3; k++) dsh[k] = SH_C0 * dRGB[k];
                 const int used = (a.degree + 1) * (a.degree + 1);
@@ -481,39 +563,32 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
                     float dRGBdx[3], dRGBdy[3], dRGBdz[3];
 #pragma unroll
                     for (int k = 0; k < 3; k++) {
-                        dsh[1 * 3 + k] = -SH_C1 * y * dRGB[k];
-                        dsh[2 * 3 + k] = SH_C1 * z * dRGB[k];
-                        dsh[3 * 3 + k] = -SH_C1 * x * dRGB[k];
                         dRGBdx[k] = -SH_C1 * sh[3 * 3 + k];
                         dRGBdy[k] = -SH_C1 * sh[1 * 3 + k];
                         dRGBdz[k] = SH_C1 * sh[2 * 3 + k];
+                        dsh[1 * 3 + k] = -SH_C1 * y * dRGB[k];
+                        dsh[2 * 3 + k] = SH_C1 * z * dRGB[k];
+                        dsh[3 * 3 + k] = -SH_C1 * x * dRGB[k];
                     }
                     if (a.degree > 1) {
                         const float xx = x * x, yy = y * y, zz = z * z, xy_ = x * y, yz = y * z, xz = x * z;
 #pragma unroll
                         for (int k = 0; k < 3; k++) {
-                            dsh[4 * 3 + k] = SH_C2[0] * xy_ * dRGB[k];
-                            dsh[5 * 3 + k] = SH_C2[1] * yz * dRGB[k];
-                            dsh[6 * 3 + k] = SH_C2[2] * (2.f * zz - xx - yy) * dRGB[k];
-                            dsh[7 * 3 + k] = SH_C2[3] * xz * dRGB[k];
-                            dsh[8 * 3 + k] = SH_C2[4] * (xx - yy) * dRGB[k];
                             dRGBdx[k] += SH_C2[0] * y * sh[4 * 3 + k] + SH_C2[2] * 2.f * -x * sh[6 * 3 + k] +
                                          SH_C2[3] * z * sh[7 * 3 + k] + SH_C2[4] * 2.f * x * sh[8 * 3 + k];
                             dRGBdy[k] += SH_C2[0] * x * sh[4 * 3 + k] + SH_C2[1] * z * sh[5 * 3 + k] +
                                          SH_C2[2] * 2.f * -y * sh[6 * 3 + k] + SH_C2[4] * 2.f * -y * sh[8 * 3 + k];
                             dRGBdz[k] += SH_C2[1] * y * sh[5 * 3 + k] + SH_C2[2] * 2.f * 2.f * z * sh[6 * 3 + k] +
                                          SH_C2[3] * x * sh[7 * 3 + k];
+                            dsh[4 * 3 + k] = SH_C2[0] * xy_ * dRGB[k];
+                            dsh[5 * 3 + k] = SH_C2[1] * yz * dRGB[k];
+                            dsh[6 * 3 + k] = SH_C2[2] * (2.f * zz - xx - yy) * dRGB[k];
+                            dsh[7 * 3 + k] = SH_C2[3] * xz * dRGB[k];
+                            dsh[8 * 3 + k] = SH_C2[4] * (xx - yy) * dRGB[k];
                         }
                         if (a.degree > 2) {
 #pragma unroll
                             for (int k = 0; k < 3; k++) {
-                                dsh[9 * 3 + k] = SH_C3[0] * y * (3.f * xx - yy) * dRGB[k];
-                                dsh[10 * 3 + k] = SH_C3[1] * xy_ * z * dRGB[k];
-                                dsh[11 * 3 + k] = SH_C3[2] * y * (4.f * zz - xx - yy) * dRGB[k];
-                                dsh[12 * 3 + k] = SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy) * dRGB[k];
-                                dsh[13 * 3 + k] = SH_C3[4] * x * (4.f * zz - xx - yy) * dRGB[k];
-                                dsh[14 * 3 + k] = SH_C3[5] * z * (xx - yy) * dRGB[k];
-                                dsh[15 * 3 + k] = SH_C3[6] * x * (xx - 3.f * yy) * dRGB[k];
                                 dRGBdx[k] += SH_C3[0] * sh[9 * 3 + k] * 3.f * 2.f * xy_ +
                                              SH_C3[1] * sh[10 * 3 + k] * yz +
                                              SH_C3[2] * sh[11 * 3 + k] * -2.f * xy_ +
@@ -533,6 +608,13 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
                                              SH_C3[3] * sh[12 * 3 + k] * 3.f * (2.f * zz - xx - yy) +
                                              SH_C3[4] * sh[13 * 3 + k] * 4.f * 2.f * xz +
                                              SH_C3[5] * sh[14 * 3 + k] * (xx - yy);
+                                dsh[9 * 3 + k] = SH_C3[0] * y * (3.f * xx - yy) * dRGB[k];
+                                dsh[10 * 3 + k] = SH_C3[1] * xy_ * z * dRGB[k];
+                                dsh[11 * 3 + k] = SH_C3[2] * y * (4.f * zz - xx - yy) * dRGB[k];
+                                dsh[12 * 3 + k] = SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy) * dRGB[k];
+                                dsh[13 * 3 + k] = SH_C3[4] * x * (4.f * zz - xx - yy) * dRGB[k];
+                                dsh[14 * 3 + k] = SH_C3[5] * z * (xx - yy) * dRGB[k];
+                                dsh[15 * 3 + k] = SH_C3[6] * x * (xx - 3.f * yy) * dRGB[k];
                             }
                         }
                     }
@@ -609,7 +691,7 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
                     for (int k = 0; k < 3; k++)
                         pose[6 + 3 * m + k] = Jm[0][m] * dMt[0][k] + Jm[1][m] * dMt[1][k];
             }
-        } else if (!a.colors_precomp && b.dshs) {
+        } else if (!WIDE && !a.colors_precomp && b.dshs) {   // (wide rows: zeros come from warp_rows_out)
             float* dsh = b.dshs + (size_t)i * a.M * 3;
             for (int m = 0; m < a.M * 3; m++) dsh[m] = 0.f;
         }
@@ -656,6 +738,13 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
         if (b.dcov3D) {
 #pragma unroll
             for (int k = 0; k < 6; k++) b.dcov3D[(size_t)6 * i + k] = dS[k];
+        }
+    }
+    if constexpr (WIDE) {
+        if (b.dshs) {
+            const long long i0w = (long long)i - (threadIdx.x & 31);
+            const int L = 3 * a.M, n = (int)max(0ll, min(32ll, (long long)a.P - i0w));
+            warp_rows_out(b.dshs, i0w, L, L | 1, n, sh_rows, sh_row - (threadIdx.x & 31) * (L | 1));
         }
     }
     if (b.route_world > 0) {   // kernel-uniform
@@ -735,14 +824,41 @@ PreArgs make_args(const EagsView& v, const EagsGaussians& g) {
     return a;
 }
 
+// SH rows wider than one coefficient go through the shared-memory staging of the <true> kernels
+inline bool wide_sh(const PreArgs& a) {
+    return a.shs && !a.colors_precomp && a.M > 1 && a.M <= SH_WIDE_MAX_M;
+}
+inline size_t wide_sh_smem(const PreArgs& a) { return (size_t)PRE_THREADS * ((3 * a.M) | 1) * sizeof(float); }
+
+// > 48 KB of dynamic shared memory is an opt-in per kernel and device
+template <typename K>
+bool allow_wide_smem(K kernel) {
+    static bool done[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+    if (!done[dev]) {
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SH_WIDE_SMEM) != cudaSuccess)
+            return false;
+        done[dev] = true;
+    }
+    return true;
+}
+
 }  // namespace
 
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
                           int32_t* radii, unsigned long long* bucket, unsigned tile_cap, cudaStream_t s) {
     if (g.P <= 0) return 0;
     PreArgs a = make_args(v, g);
-    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(
-        a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
+    const int grid = (g.P + PRE_THREADS - 1) / PRE_THREADS;
+    if (wide_sh(a)) {
+        if (!allow_wide_smem(preprocess_fwd_kernel<true>)) return -1;
+        preprocess_fwd_kernel<true><<<grid, PRE_THREADS, wide_sh_smem(a), s>>>(
+            a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
+    } else {
+        preprocess_fwd_kernel<false><<<grid, PRE_THREADS, 0, s>>>(
+            a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
+    }
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
@@ -780,7 +896,13 @@ int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32
         if (route->accum[0])
             for (int k = 0; k < 4; k++) b.route_acc[k] = route->accum[k];
     }
-    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(a, b);
+    const int grid = (g.P + PRE_THREADS - 1) / PRE_THREADS;
+    if (wide_sh(a)) {
+        if (!allow_wide_smem(preprocess_bwd_kernel<true>)) return -1;
+        preprocess_bwd_kernel<true><<<grid, PRE_THREADS, wide_sh_smem(a), s>>>(a, b);
+    } else {
+        preprocess_bwd_kernel<false><<<grid, PRE_THREADS, 0, s>>>(a, b);
+    }
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
     int n = 1;
     if (gout.dL_dtau) {

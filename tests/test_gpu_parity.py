@@ -24,6 +24,8 @@ CASES = [
     ("tiny", None, 1, 0, 0, (0, 0, 0), (0, 0)),
     ("ragged", None, 4, 1, 1, (0.1, 0.2, 0.3), (3, -2)),
     ("ragged", 3000, 16, 3, 0, (0.3, 0.1, 0.2), (-2, 4)),
+    ("ragged", 2011, 9, 2, 0, (0, 0, 0), (1, -3)),      # 27-float SH rows (odd), P not a multiple of 32
+    ("ragged", 1000, 16, 1, 1, (0, 0, 0), (0, 2)),      # more coefficients than the active degree uses
     ("c1", 50_000, 1, 0, 0, (0, 0, 0), (0, 0)),
     ("c1", 20_000, 1, 0, 1, (0, 0, 0), (1, 1)),
 ]
@@ -108,6 +110,12 @@ def test_forward_backward_parity(wl, P, M, degree, variant, bg, rot, tma):
         # culled Gaussians get exactly zero gradient
         cul = o["radii"] == 0
         assert np.all(_np(got["means3D"])[cul] == 0) and np.all(_np(got["shs"])[cul] == 0)
+        if degree > 0:
+            # frozen SH features: dL/dmeans3D still carries the view-direction term of the SH colour
+            frozen = rasterize_backward(st, state, d["means3D"], d["opacities"], d["shs"], None, d["scales"],
+                                        d["rotations"], None, dC.cuda(), dD.cuda(), dA.cuda(), want_shs=False)
+            assert frozen["shs"] is None
+            assert rel_err(_np(frozen["means3D"]), ref["dL_dmeans3D"]) < RTOL_GRAD
     finally:
         _lib.set_option("tma", 1)
 
