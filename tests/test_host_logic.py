@@ -54,3 +54,54 @@ def test_capture_ctx_hands_out_each_status_block_once():
     assert a.data_ptr() != b.data_ptr() and [c for _, c in ctx.used] == [10, 20]
     with pytest.raises(RuntimeError, match="max_renders"):
         ctx.take_status(30)
+
+
+def test_sharded_mapper_splits_parameters_between_exchange_and_bucket():
+    """Host logic of ShardedMapper(exchange=...): routed parameters stay out of the NCCL bucket, get their
+    gradient from the routed pass only, and the route is opened for exactly the rank's views (a stand-in
+    exchange records the calls; the real one needs a GPU: tests/test_gpu_peer.py)."""
+    from eags_raster import sharded
+
+    class FakeRoute:
+        def __init__(self, log, **kw):
+            self.log, self.kw = log, kw
+
+        def __enter__(self):
+            self.log.append(("enter", self.kw))
+
+        def __exit__(self, *exc):
+            self.log.append(("exit", None))
+            return False
+
+    class FakeExchange:
+        def __init__(self):
+            self.log = []
+
+        def route(self, **kw):
+            return FakeRoute(self.log, **kw)
+
+    xyz = torch.zeros(5, 3, requires_grad=True)
+    feat = torch.ones(5, 3, requires_grad=True)
+    xyz.grad = torch.full((5, 3), 7.0)           # stale gradient of an earlier step
+    opt = torch.optim.SGD([xyz, feat], lr=0.5)
+    ex = FakeExchange()
+    m = sharded.ShardedMapper([xyz, feat], opt, broadcast=False, exchange=ex, exchanged=[xyz])
+    assert [id(p) for p in m.bucket.params] == [id(feat)]
+    seen = []
+
+    def loss_fn(v):
+        seen.append(v)
+        assert xyz.grad is None or not torch.any(xyz.grad == 7.0)      # cleared before the first pass
+        return (xyz.sum() + feat.sum()) * float(v)
+
+    out = m.step([1.0, 2.0, 3.0], loss_fn)
+    assert seen == [1.0, 2.0, 3.0] and out["local_views"] == 3
+    assert ex.log[0] == ("enter", {"scale": 1.0 / 3, "local_views": 3}) and ex.log[-1][0] == "exit"
+    # the bucket parameter carries the mean over views (world 1): (1 + 2 + 3) / 3 = 2 -> 1 - 0.5 * 2 = 0
+    assert torch.allclose(feat.detach(), torch.zeros(5, 3))
+    with pytest.raises(ValueError, match="needs exchange"):
+        sharded.ShardedMapper([xyz], opt, broadcast=False, exchanged=[xyz])
+    # all parameters routed: no bucket, no NCCL call
+    m2 = sharded.ShardedMapper([xyz], torch.optim.SGD([xyz], lr=0.1), broadcast=False, exchange=ex, exchanged=[xyz])
+    assert m2.bucket is None
+    m2.step([1.0], lambda v: xyz.sum())
