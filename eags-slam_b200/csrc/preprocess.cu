@@ -213,19 +213,36 @@ constexpr int SH_WIDE_MAX_M = 16;
 constexpr int SH_WIDE_STRIDE_MAX = (3 * SH_WIDE_MAX_M) | 1;
 constexpr size_t SH_WIDE_SMEM = (size_t)PRE_THREADS * SH_WIDE_STRIDE_MAX * sizeof(float);
 
-// rows (bit r of `rows` set) of the warp whose first Gaussian is i0w: global -> shared
-__device__ __forceinline__ void warp_rows_in(const float* __restrict__ g, long long i0w, int L, int S,
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gmem_src) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(gmem_src) : "memory");
+}
+
+// rows (bit r of `rows` set; n = rows of the warp inside the cloud) of the warp whose first Gaussian is
+// i0w: global -> shared.  Asynchronous 4-byte copies (the odd row stride rules out wider ones): nothing
+// waits until every row of the warp is in flight.
+__device__ __forceinline__ void warp_rows_in(const float* __restrict__ g, long long i0w, int L, int S, int n,
                                              unsigned rows, float* s_w) {
     const int lane = threadIdx.x & 31;
-    while (rows) {
-        const int r = __ffs(rows) - 1;
-        rows &= rows - 1;
-        const float* src = g + (size_t)(i0w + r) * L;
-        // asynchronous 4-byte copies (the odd row stride rules out wider ones): nothing waits until
-        // every row of the warp is in flight
-        for (int j = lane; j < L; j += 32) {
-            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_w + r * S + j);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + j) : "memory");
+    if (4 * __popc(rows) >= 3 * n) {
+        // most rows are wanted: the warp's rows are one contiguous run of n * L floats
+        const float* src = g + (size_t)i0w * L;
+        const int total = n * L;
+        int off = lane;                      // row * S + col, advanced without a division
+        int col = lane;
+        while (col >= L) { col -= L; off += S - L; }
+#pragma unroll 4
+        for (int idx = lane; idx < total; idx += 32) {
+            cp_async4(s_w + off, src + idx);
+            col += 32; off += 32;
+            while (col >= L) { col -= L; off += S - L; }
+        }
+    } else {
+        while (rows) {
+            const int r = __ffs(rows) - 1;
+            rows &= rows - 1;
+            const float* src = g + (size_t)(i0w + r) * L;
+            for (int j = lane; j < L; j += 32) cp_async4(s_w + r * S + j, src + j);
         }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -233,16 +250,20 @@ __device__ __forceinline__ void warp_rows_in(const float* __restrict__ g, long l
     __syncwarp();
 }
 
-// all `n` rows of the warp: shared (rows in `rows`) or zeros -> global
+// all `n` rows of the warp: shared (rows in `rows`) or zeros -> global, as one contiguous run
 __device__ __forceinline__ void warp_rows_out(float* __restrict__ g, long long i0w, int L, int S, int n,
                                               unsigned rows, const float* s_w) {
     const int lane = threadIdx.x & 31;
     __syncwarp();
+    float* dst = g + (size_t)i0w * L;
+    const int total = n * L;
+    int off = lane, col = lane, row = 0;
+    while (col >= L) { col -= L; off += S - L; row++; }
 #pragma unroll 4
-    for (int r = 0; r < n; r++) {
-        float* dst = g + (size_t)(i0w + r) * L;
-        const bool live = (rows >> r) & 1u;
-        for (int j = lane; j < L; j += 32) dst[j] = live ? s_w[r * S + j] : 0.f;
+    for (int idx = lane; idx < total; idx += 32) {
+        dst[idx] = ((rows >> row) & 1u) ? s_w[off] : 0.f;
+        col += 32; off += 32;
+        while (col >= L) { col -= L; off += S - L; row++; }
     }
 }
 
@@ -307,7 +328,9 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     if constexpr (WIDE) {
         const int L = 3 * a.M, S = L | 1;
         float* s_w = s_sh + (size_t)(threadIdx.x >> 5) * 32 * S;
-        warp_rows_in(a.shs, (long long)i - (threadIdx.x & 31), L, S, __ballot_sync(0xffffffffu, alive), s_w);
+        const long long i0w = (long long)i - (threadIdx.x & 31);
+        warp_rows_in(a.shs, i0w, L, S, (int)max(0ll, min(32ll, (long long)a.P - i0w)),
+                     __ballot_sync(0xffffffffu, alive), s_w);
         sh_row = s_w + (threadIdx.x & 31) * S;
     } else if (alive && !a.colors_precomp) {
         sh_row = a.shs + (size_t)i * a.M * 3;
@@ -449,7 +472,8 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
         const int L = 3 * a.M, S = L | 1;
         float* s_w = s_sh + (size_t)(threadIdx.x >> 5) * 32 * S;
         sh_rows = __ballot_sync(0xffffffffu, vis);
-        warp_rows_in(a.shs, (long long)i - (threadIdx.x & 31), L, S, sh_rows, s_w);
+        const long long i0w = (long long)i - (threadIdx.x & 31);
+        warp_rows_in(a.shs, i0w, L, S, (int)max(0ll, min(32ll, (long long)a.P - i0w)), sh_rows, s_w);
         sh_row = s_w + (threadIdx.x & 31) * S;
     }
     float pose[15];
