@@ -26,6 +26,7 @@ CASES = [
     ("ragged", 3000, 16, 3, 0, (0.3, 0.1, 0.2), (-2, 4)),
     ("ragged", 2011, 9, 2, 0, (0, 0, 0), (1, -3)),      # 27-float SH rows (odd), P not a multiple of 32
     ("ragged", 1000, 16, 1, 1, (0, 0, 0), (0, 2)),      # more coefficients than the active degree uses
+    ("ragged", 3000, 16, 3, 0, (0, 0, 0), (25, 10)),    # 58 % visible: sparse warps fetch SH rows one by one
     ("c1", 50_000, 1, 0, 0, (0, 0, 0), (0, 0)),
     ("c1", 20_000, 1, 0, 1, (0, 0, 0), (1, 1)),
 ]
