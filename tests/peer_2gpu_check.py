@@ -103,7 +103,69 @@ for it in range(4):
         dist.broadcast(c, src=0)
         assert torch.equal(c, g[k]), ("graph", it, k, "replicas differ")
 assert ex.error_flag() == 0
+
+# several views per rank per step through ShardedMapper: the peer exchange (xyz / scaling / rotation /
+# opacity; the rank's first view stays local, the second carries the sum) + NCCL for the SH features,
+# against the pure NCCL mapper on identical replicas.  One SGD step each; parameters must agree.
+from eags_raster import sharded  # noqa: E402
+
+all_views = scene.keyframe_views("c1", 8)[:2 * world]
+
+
+def settings_of(c):
+    return GaussianRasterizationSettings(
+        image_height=c.H, image_width=c.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=torch.zeros(3, device=dev),
+        scale_modifier=1.0, viewmatrix=c.viewmatrix.to(dev), projmatrix=c.projmatrix.to(dev), sh_degree=0,
+        campos=c.campos.to(dev), prefiltered=False, debug=False)
+
+
+rasters = [GaussianRasterizer(raster_settings=settings_of(c)) for c in all_views]
+
+
+def make_params():
+    return {"xyz": d["means3D"].clone().requires_grad_(True), "scaling": d["scales"].log().requires_grad_(True),
+            "rotation": (d["rotations"] * 1.3).clone().requires_grad_(True),
+            "opacity": torch.logit(d["opacities"].clamp(1e-4, 1 - 1e-4)).requires_grad_(True),
+            "features": d["shs"].clone().requires_grad_(True)}
+
+
+def make_loss(prm):
+    def loss_fn(v):
+        m2d = torch.zeros_like(prm["xyz"], requires_grad=True)
+        color, depth, alpha, radii = rasters[v](
+            means3D=prm["xyz"], means2D=m2d, opacities=torch.sigmoid(prm["opacity"]), shs=prm["features"],
+            colors_precomp=None, scales=torch.exp(prm["scaling"]),
+            rotations=torch.nn.functional.normalize(prm["rotation"]), cov3D_precomp=None)
+        return (color - d["gt_color"]).abs().mean() + (depth - d["gt_depth"]).abs().mean()
+    return loss_fn
+
+
+pa, pb = make_params(), make_params()
+oa = torch.optim.SGD(list(pa.values()), lr=1e-2)
+ob = torch.optim.SGD(list(pb.values()), lr=1e-2)
+ma = sharded.ShardedMapper(list(pa.values()), oa, exchange=ex,
+                           exchanged=[pa["xyz"], pa["scaling"], pa["rotation"], pa["opacity"]])
+mb = sharded.ShardedMapper(list(pb.values()), ob)
+views = list(range(len(all_views)))
+for it in range(2):
+    ra = ma.step(views, make_loss(pa), reg_fn=lambda: 0.1 * torch.exp(pa["scaling"]).mean())
+    rb = mb.step(views, make_loss(pb), reg_fn=lambda: 0.1 * torch.exp(pb["scaling"]).mean())
+    assert ra["local_views"] == rb["local_views"] == 2
+    torch.cuda.synchronize()
+    for k in pa:
+        ga, gb = pa[k].grad, pb[k].grad
+        err, ref = float((ga - gb).abs().max()), float(gb.abs().max())
+        assert err <= 2e-5 * ref + 1e-12, ("mapper grad", it, k, err, ref)
+        c = pa[k].detach().clone()
+        dist.broadcast(c, src=0)
+        assert torch.equal(c, pa[k].detach()), ("mapper", it, k, "replicas differ")
+    # keep both mappers on the same trajectory (their gradients differ by summation order only)
+    with torch.no_grad():
+        for k in pa:
+            pb[k].copy_(pa[k])
+assert ex.error_flag() == 0
 dist.barrier()
 if rank == 0:
+    print(f"sharded mapper ok: {len(views)} views on {world} ranks (2 per rank), peer exchange + NCCL features vs NCCL only")
     print(f"peer exchange ok: world {world}, P {P}, 3 eager steps + 4 graph replays, max rel diff vs NCCL <= 1e-5, replicas bit-identical")
 dist.destroy_process_group()
