@@ -59,10 +59,12 @@ class ClockSampler:
         self.index, self.proc, self.lines = index, None, []
 
     def start(self):
+        if os.environ.get("EAGS_BENCH_CLOCKS", "smi") == "off":      # A/B knob: does the polling perturb the run?
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
-                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", os.environ.get("EAGS_BENCH_CLOCKS_MS", "20")], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -353,26 +355,42 @@ def run_ours(args):
     ring_views = [views_of(f) for f in ring]
     loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
 
+    # EAGS_BENCH_E2E_SPLIT=k splits the block over k copy streams (A/B knob; one stream is the default)
+    nsplit = max(1, int(os.environ.get("EAGS_BENCH_E2E_SPLIT", "1")))
+    copy_streams = [copy_stream] + [torch.cuda.Stream(device=dev) for _ in range(nsplit - 1)]
+    bounds = [host_flat.numel() * c // nsplit for c in range(nsplit + 1)]
+    copy_times = [] if os.environ.get("EAGS_BENCH_E2E_TRACE") else None
+
     def prefetch(j):
-        with torch.cuda.stream(copy_stream):
-            if ring_free[j] is not None:
-                copy_stream.wait_event(ring_free[j])
-            ring[j].copy_(host_flat, non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(copy_stream)
-        return ev
+        evs = []
+        for c, cs in enumerate(copy_streams):
+            with torch.cuda.stream(cs):
+                if ring_free[j] is not None:
+                    cs.wait_event(ring_free[j])
+                if copy_times is not None and c == 0:
+                    t_a = torch.cuda.Event(enable_timing=True)
+                    t_a.record(cs)
+                ring[j][bounds[c]:bounds[c + 1]].copy_(host_flat[bounds[c]:bounds[c + 1]], non_blocking=True)
+                ev = torch.cuda.Event(enable_timing=copy_times is not None and c == 0)
+                ev.record(cs)
+                if copy_times is not None and c == 0:
+                    copy_times.append((t_a, ev))
+            evs.append(ev)
+        return evs
 
     def e2e_loop(n, depth=2):
         for j in range(RING):
             ring_free[j] = None
         q = [prefetch(i % RING) for i in range(min(depth, n))]
         pending, losses_read = None, []
+        trace = [] if os.environ.get("EAGS_BENCH_E2E_TRACE") else None
         for i in range(n):
             ev = q.pop(0)
             if i + depth < n:
                 q.append(prefetch((i + depth) % RING))
             cur = torch.cuda.current_stream()
-            cur.wait_event(ev)
+            for e_ in ev:
+                cur.wait_event(e_)
             if use_graph:     # this step's inputs: ring slot -> the graph's static input block (D2D)
                 static_flat.copy_(ring[i % RING], non_blocking=True)
                 loss = gi.replay()
@@ -387,14 +405,24 @@ def run_ours(args):
             if pending is not None:
                 pending[0].synchronize()
                 losses_read.append(float(pending[1]))
+                if trace is not None:
+                    trace.append(time.perf_counter())
             pending = (done, loss_host[i % 2])
         if pending is not None:
             pending[0].synchronize()
             losses_read.append(float(pending[1]))
         assert len(losses_read) == n and all(v == v for v in losses_read)
+        if trace:
+            print("[e2e trace] ms between consecutive step completions:",
+                  " ".join(f"{(b - a) * 1e3:.2f}" for a, b in zip(trace[:40], trace[1:41])), file=sys.stderr, flush=True)
+            torch.cuda.synchronize()
+            d = sorted(a.elapsed_time(b) for a, b in copy_times)
+            print(f"[e2e trace] H2D copy on stream 0 ({(bounds[1] - bounds[0]) * 4 / 1e6:.1f} MB of {nsplit} split(s)): "
+                  f"min {d[0]:.3f} median {d[len(d) // 2]:.3f} max {d[-1]:.3f} ms", file=sys.stderr, flush=True)
+            copy_times.clear()
 
     _stamp("eager comparison done")
-    e2e_loop(3)
+    e2e_loop(20)      # the host pipeline needs ~20 steps to settle (per-step trace: EAGS_BENCH_E2E_TRACE=1)
     barrier()
     t0 = time.perf_counter()
     e2e_loop(args.steps)
