@@ -93,3 +93,44 @@ def test_losses_refuse_cpu_tensors():
     z = torch.zeros(3, 4, 4)
     with pytest.raises(RuntimeError, match="no CPU path"):
         masked_l1_means(z, z[:1], z, z[:1])
+
+
+# ---- pinned by the reference's own l1_loss, combined as its call sites combine it -------------------
+# tests/golden/losses_reference.npz (make_golden_losses.py: tracker.py:112-126, mapper.py:160-165, fp32 CPU
+# torch + autograd).  Values 1e-5 relative; gradients 1e-5 relative to the largest reference gradient.
+def _golden():
+    import os
+    import numpy as np
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "losses_reference.npz"))
+
+
+@pytest.mark.parametrize("tag,soft_alpha,mask_color", [("soft", True, False), ("soft_masked", True, True),
+                                                       ("hard", False, False)])
+def test_tracking_losses_against_reference_vectors(tag, soft_alpha, mask_color):
+    from eags_raster.losses import tracking_losses
+    g = _golden()
+    t = {k: torch.from_numpy(g[k]).to(DEV) for k in ("color", "depth", "alpha", "gt_color", "gt_depth", "tracking_mask")}
+    c, d, a = (t[k].clone().requires_grad_(True) for k in ("color", "depth", "alpha"))
+    lc, ld = tracking_losses(c, d, a, t["gt_color"], t["gt_depth"], t["tracking_mask"], soft_alpha=soft_alpha,
+                             mask_invalid_depth_in_color_loss=mask_color)
+    (0.7 * lc + 1.3 * ld).backward()
+    rc, rd = float(g[f"track_{tag}_color_loss"]), float(g[f"track_{tag}_depth_loss"])
+    assert abs(float(lc) - rc) <= 1e-5 * abs(rc) and abs(float(ld) - rd) <= 1e-5 * abs(rd)
+    for leaf, key in ((c, "dcolor"), (d, "ddepth"), (a, "dalpha")):
+        ref = torch.from_numpy(g[f"track_{tag}_{key}"]).to(DEV)
+        got = leaf.grad if leaf.grad is not None else torch.zeros_like(ref)
+        assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max()) + 1e-12, key
+
+
+def test_masked_l1_means_against_reference_vectors():
+    from eags_raster.losses import masked_l1_means
+    g = _golden()
+    t = {k: torch.from_numpy(g[k]).to(DEV) for k in ("color", "depth", "gt_color", "gt_depth", "map_mask")}
+    c, d = t["color"].clone().requires_grad_(True), t["depth"].clone().requires_grad_(True)
+    lc, ld = masked_l1_means(c, d, t["gt_color"], t["gt_depth"], t["map_mask"])
+    (lc + ld).backward()
+    assert abs(float(lc) - float(g["map_color_l1"])) <= 1e-5 * float(g["map_color_l1"])
+    assert abs(float(ld) - float(g["map_depth_l1"])) <= 1e-5 * float(g["map_depth_l1"])
+    for leaf, key in ((c, "map_dcolor"), (d, "map_ddepth")):
+        ref = torch.from_numpy(g[key]).to(DEV)
+        assert float((leaf.grad - ref).abs().max()) <= 1e-5 * float(ref.abs().max()), key
