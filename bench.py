@@ -144,6 +144,38 @@ def pin_to_gpu_numa_node(index):
     return None, None
 
 
+_HOST_BLOCKS = []     # (mmap, pointer) of huge-page staging blocks: kept alive for the life of the process
+
+
+def pinned_host_block(numel):
+    """Pinned fp32 staging block for the e2e leg.  Anonymous mmap + MADV_HUGEPAGE + cudaHostRegister: alone on a
+    B200 box the first ~10 copies out of a 4-KiB-page cudaHostAlloc block (torch ``pin_memory()``) take 0.5 - 8 ms
+    per 16.8 MB while the huge-page block streams at 54 GB/s from the first copy on (profiles/r1c/h2d_ab.txt);
+    in steady state both are equal, and inside bench.py the A/B shows no difference (the slow phases of
+    profiles/r1c/e2e_h2d_variance.txt hit both).  EAGS_BENCH_HOSTMEM=torch, or any failure, falls back to
+    ``pin_memory()``.  Returns (tensor, kind)."""
+    if os.environ.get("EAGS_BENCH_HOSTMEM", "hugepage") != "torch":
+        try:
+            import mmap
+            import numpy as np
+            huge = 2 << 20
+            size = ((numel * 4 + huge - 1) // huge + 1) * huge
+            m = mmap.mmap(-1, size, flags=mmap.MAP_PRIVATE | mmap.MAP_ANONYMOUS)
+            m.madvise(mmap.MADV_HUGEPAGE)
+            arr = np.frombuffer(m, dtype=np.float32)
+            off = (-arr.ctypes.data % huge) // 4
+            arr = arr[off:off + numel]
+            arr[:] = 0.0                                            # touch: populate the (huge) pages
+            t = torch.from_numpy(arr)
+            rc = torch.cuda.cudart().cudaHostRegister(t.data_ptr(), numel * 4, 0)
+            if int(rc) == 0 and t.is_pinned():
+                _HOST_BLOCKS.append((m, t.data_ptr()))
+                return t, "mmap + MADV_HUGEPAGE + cudaHostRegister"
+        except Exception:                                           # noqa: BLE001
+            pass
+    return torch.empty(numel, dtype=torch.float32).pin_memory(), "torch pin_memory (cudaHostAlloc)"
+
+
 def run_ours(args):
     import torch.distributed as dist
     from eags_raster import _lib, rasterize as rz, state_array
@@ -339,7 +371,7 @@ def run_ours(args):
     # All five Gaussian tensors live in ONE pinned host block and cross PCIe as one copy per step (the
     # step is PCIe-bound: 56 B/Gaussian at ~25 GB/s is longer than the kernels); the copies run two
     # steps ahead on a copy stream so the link never idles while the host reads the loss back.
-    host_flat = torch.empty(sum(sizes_h), dtype=torch.float32).pin_memory()
+    host_flat, hostmem_kind = pinned_host_block(sum(sizes_h))
     o = 0
     for k, n_ in zip(order, sizes_h):
         host_flat[o:o + n_].copy_(host[k].reshape(-1))
@@ -454,6 +486,7 @@ def run_ours(args):
                        "parallelism": "1 view/GPU, replica per GPU" + (", gradient exchange of 11 floats/Gaussian: " + collective if world > 1 else "")},
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms,
+                    "host_block": hostmem_kind,
                     "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
             "gpu_launches": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
