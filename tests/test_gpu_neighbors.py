@@ -105,3 +105,16 @@ def test_compute_new_points_ids_edge_cases():
     assert ids.tolist() == list(range(10))
     ids = compute_new_points_ids(new.cpu(), new.cpu(), radius=0.03, device="cuda")
     assert ids.numel() == 0
+
+
+@pytest.mark.parametrize("c", range(1, 6))
+def test_compute_new_points_ids_against_reference_vectors(c):
+    """Kept indices equal the ones the reference's own compute_new_points_ids produced
+    (tests/golden/neighbors_reference.npz, make_golden_neighbors.py; borderline queries were re-drawn there)."""
+    import os
+    from eags_raster.neighbors import compute_new_points_ids
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "neighbors_reference.npz"))
+    ref, new = torch.from_numpy(g[f"{c}/ref"]).cuda(), torch.from_numpy(g[f"{c}/new"]).cuda()
+    ids = compute_new_points_ids(ref, new, radius=float(g[f"{c}/radius"]), device="cuda")
+    assert ids.dtype == torch.int64
+    assert np.array_equal(ids.cpu().numpy(), g[f"{c}/ids"])

@@ -37,3 +37,13 @@ def test_new_points_rule_is_squared_distance_below_radius():
     assert np.allclose(d, [0.01, 0.04, 0.0289, 0.0324], rtol=1e-5)
     ids, d = nb.new_points_ids(np.zeros((0, 3), np.float32), q)
     assert ids.tolist() == [0, 1, 2, 3] and d is None
+
+
+def test_new_points_rule_against_reference_vectors():
+    """tests/golden/neighbors_reference.npz: the reference's own compute_new_points_ids (mapper_utils.py:193-226)
+    run over an exact brute-force stand-in for faiss.IndexFlatL2 (make_golden_neighbors.py)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "neighbors_reference.npz"))
+    for c in range(1, 6):
+        ids, _ = nb.new_points_ids(g[f"{c}/ref"], g[f"{c}/new"], radius=float(g[f"{c}/radius"]))
+        assert np.array_equal(ids, g[f"{c}/ids"]), c
