@@ -3,7 +3,9 @@
 with this repo's packages answering `from gaussian_rasterizer import ...` (utils.py:8), its
 get_render_settings builds the shim's settings tuple, and its render_gaussian_model (utils.py:120-186) reaches
 the operator with the reference's own keyword set; likewise src/gsr/renderer.py::render (variant B, with
-src/gsr/camera.py's Camera and `from simple_knn._C import distCUDA2` of gaussian_model.py:17).  There is no GPU here, so the call must fail LOUDLY in the
+src/gsr/camera.py's Camera and `from simple_knn._C import distCUDA2` of gaussian_model.py:17).  Last, the submap
+hand-off layout: the reference's own Submap.load reads what handoff.to_ckpt wrote and
+handoff packs what the reference's Submap.save wrote.  There is no GPU here, so the call must fail LOUDLY in the
 shim (no CPU fallback) - which also proves the reference's caller got all the way to the boundary.
 Runs in a subprocess so the reference's `src` package and the open3d stand-in never enter the test process."""
 import os
@@ -78,12 +80,40 @@ SCRIPT = textwrap.dedent("""
         print("LOUD-B:", e)
     else:
         raise SystemExit("gsr.renderer.render returned on CPU tensors: a CPU fallback exists")
+
+    # ---- submap hand-off (SURVEY 8(f) N-4): the reference's own Submap.save / Submap.load on the same layout ----
+    import os, pathlib, tempfile
+    for name in ("roma", "wandb"):                              # imported by submap.py / io_utils.py, unused here
+        sys.modules[name] = types.ModuleType(name)
+    from src.entities.submap import Submap
+    from eags_raster import handoff
+    P = 321
+    g = torch.Generator().manual_seed(9)
+    sub = {"id": 7,
+           "gaussian_params": {"xyz": torch.randn(P, 3, generator=g), "features_dc": torch.randn(P, 1, 3, generator=g),
+                               "features_rest": torch.zeros(P, 0, 3), "scaling": torch.randn(P, 3, generator=g),
+                               "rotation": torch.randn(P, 4, generator=g), "opacity": torch.randn(P, 1, generator=g)},
+           "Tmc": torch.eye(4, dtype=torch.float64)[None].repeat(4, 1, 1), "kf_id": torch.arange(20, 24),
+           "T_prev_m": torch.eye(4, dtype=torch.float64)}
+    with tempfile.TemporaryDirectory() as d:
+        path = handoff.to_ckpt(sub, d)                          # this repo writes ...
+        back = Submap().load(path, device="cpu")                # ... the reference's loader reads (submap.py:21-37)
+        assert back.id == 7 and torch.equal(back.kf_id, sub["kf_id"]) and torch.equal(back.Tmc, sub["Tmc"])
+        assert all(torch.equal(back.gaussian_params[k], v) for k, v in sub["gaussian_params"].items())
+        back.id = 8
+        back.save(pathlib.Path(d) / "ref")                      # the reference writes (submap.py:109-124) ...
+        theirs = torch.load(os.path.join(d, "ref", "000008.ckpt"), weights_only=False)
+        assert tuple(theirs) == handoff.CKPT_KEYS
+        handoff.check_layout(theirs)                            # ... this repo packs / unpacks
+        again = handoff.unpack(*handoff.pack(theirs))
+        assert again["id"] == 8 and all(torch.equal(again["gaussian_params"][k], v) for k, v in sub["gaussian_params"].items())
+    print("HANDOFF ok")
 """)
 
 
 @pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="reference checkout not present")
-def test_reference_callers_reach_the_shims_and_fail_loudly_without_a_gpu():
+def test_reference_callers_reach_the_shims_fail_loudly_without_a_gpu_and_share_the_submap_layout():
     code = SCRIPT % dict(ref=REF, pkg=os.path.join(ROOT, "eags-slam_b200"), root=ROOT)
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert "LOUD:" in r.stdout and "LOUD-B:" in r.stdout
+    assert "LOUD:" in r.stdout and "LOUD-B:" in r.stdout and "HANDOFF ok" in r.stdout
