@@ -1,10 +1,12 @@
-"""Round-2 experiment (NOT yet run on a GPU: the round-1 budget ended here): per-copy time of the e2e block's
+"""Per-copy time of the e2e block's
 host->device copy (16.8 MB, bench.py's e2e leg) while THIS repo's iteration graph replays on the compute stream,
 with and without the per-step 16.8 MB device-to-device copy bench.py issues before each replay.
 
 profiles/r1c/h2d_ab.txt shows the copy alone (idle, or under tensor-core matmuls) at a steady 0.310 ms from
 4-KiB and from huge pages; profiles/r1c/e2e_h2d_variance.txt shows it at 0.31 ... 1.36 ms inside bench.py.  This
-script separates "our kernels / our D2D copy disturb the DMA" from "the box's host side is busy":
+script separates "our kernels / our D2D copy disturb the DMA" from "the box's host side is busy".  Result
+(profiles/r1c/h2d_under_raster.txt, last GPU seconds of round 1): 0.311 ms per copy (54 GB/s) idle, under graph
+replay and under replay + D2D copy, from 4-KiB and from huge pages alike -> the GPU-side load is not the cause.
 
     python profiles/h2d_under_raster.py          # prints min / p10 / median / p90 / max per phase
 """
