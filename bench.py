@@ -368,8 +368,9 @@ def run_ours(args):
     # Input pipeline: the copy of step i+1's inputs is issued on a copy stream while step i computes
     # (double buffering, as a data loader would); every step's inputs cross PCIe inside the timed
     # region and the loss is read back (host sync) every step.
-    # All five Gaussian tensors live in ONE pinned host block and cross PCIe as one copy per step (the
-    # step is PCIe-bound: 56 B/Gaussian at ~25 GB/s is longer than the kernels); the copies run two
+    # All five Gaussian tensors live in ONE pinned host block and cross PCIe as one copy per step (56 B /
+    # Gaussian: 0.31 ms at the link's 54 GB/s, shorter than the kernels; up to 1.4 ms when the host side of
+    # the shared box is busy, and then the step is copy-bound -- see link_rate below); the copies run two
     # steps ahead on a copy stream so the link never idles while the host reads the loss back.
     host_flat, hostmem_kind = pinned_host_block(sum(sizes_h))
     o = 0
@@ -453,13 +454,36 @@ def run_ours(args):
                   f"min {d[0]:.3f} median {d[len(d) // 2]:.3f} max {d[-1]:.3f} ms", file=sys.stderr, flush=True)
             copy_times.clear()
 
+    def link_rate(reps=10):
+        """The same block, copied alone (nothing else queued), CUDA events on the copy stream: the host->device
+        rate the box delivers right now.  The e2e step is max(copy, compute); on the shared boxes the copy moves
+        between 0.31 and 1.4 ms (profiles/r1c/e2e_h2d_variance.txt), so every e2e number carries this figure."""
+        try:
+            torch.cuda.synchronize()
+            with torch.cuda.stream(copy_stream):
+                pairs = []
+                for _ in range(reps):
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(copy_stream)
+                    ring[0].copy_(host_flat, non_blocking=True)
+                    b.record(copy_stream)
+                    pairs.append((a, b))
+            copy_stream.synchronize()
+            t = sorted(a.elapsed_time(b) for a, b in pairs)
+            return {"median_ms": t[len(t) // 2], "min_ms": t[0], "max_ms": t[-1],
+                    "median_gbs": h2d_bytes / t[len(t) // 2] / 1e6}
+        except Exception as e:                                      # noqa: BLE001
+            return {"error": f"{type(e).__name__}: {str(e)[:100]}"}
+
     _stamp("eager comparison done")
     e2e_loop(20)      # the host pipeline needs ~20 steps to settle (per-step trace: EAGS_BENCH_E2E_TRACE=1)
+    link_before = link_rate()
     barrier()
     t0 = time.perf_counter()
     e2e_loop(args.steps)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    link_after = link_rate()
     if use_graph:
         gi.check()
     _stamp("e2e done")
@@ -487,6 +511,8 @@ def run_ours(args):
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms,
                     "host_block": hostmem_kind,
+                    "h2d_copy_alone": {"before": link_before, "after": link_after,
+                                       "note": "the step's block copied alone right before / after the e2e leg"},
                     "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
             "gpu_launches": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
