@@ -514,7 +514,9 @@ def run_ours(args):
                     "h2d_copy_alone": {"before": link_before, "after": link_after,
                                        "note": "the step's block copied alone right before / after the e2e leg"},
                     "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
-            "gpu_launches": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
+            # kernels of this repo launched inside the timed region (counted by the C ABI's launch counter:
+            # per step x steps; under graph replay each replay launches the captured kernels once)
+            "gpu_launches": int(round(launches * args.steps)), "gpu_launches_per_step": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks, "roofline": roof, "kernels": kern,
         }
