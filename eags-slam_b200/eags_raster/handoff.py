@@ -7,11 +7,12 @@ file: ``Submap.save`` writes ``{id, gaussian_params, Tmc, kf_id, T_prev_m}`` wit
 latency.  Here the same dictionary travels
 
 * inside one process (the reference's layout: main thread on device 0, LC thread on ``lc.device``)
-  through :class:`SubmapMailbox`: all tensors are packed into ONE contiguous block per dtype, moved
-  with one device-to-device copy over NVLink (peer copy) and re-viewed on the destination -- no
+  through :class:`SubmapMailbox`: all tensors are packed into ONE contiguous block per (dtype, source
+  device) -- the reference's dictionary mixes GPU and CPU tensors -- each moved with one copy
+  (device-to-device over NVLink for the Gaussian parameters) and re-viewed on the destination -- no
   serialisation, no host bounce;
 * between ranks (one process per GPU) through :func:`send_submap` / :func:`recv_submap`:
-  a small pickled header plus one ``torch.distributed`` send per dtype block (NCCL P2P on GPUs, gloo
+  a small pickled header plus one ``torch.distributed`` send per block (NCCL P2P on GPUs, gloo
   in the CPU tests).
 
 The dictionary layout is exactly the checkpoint's, so ``to_ckpt`` still writes a file the
@@ -59,29 +60,36 @@ def _set(root: Any, path: Tuple, value: Any):
     root[path[-1]] = value
 
 
-def pack(submap: Dict) -> Tuple[Dict, Dict[torch.dtype, torch.Tensor]]:
-    """-> (header, {dtype: one contiguous 1-D block}).  The header records, for every tensor, its
-    path, dtype, shape and offset inside its dtype block."""
-    entries, chunks = [], {}
+def pack(submap: Dict) -> Tuple[Dict, List[torch.Tensor]]:
+    """-> (header, blocks).  Tensors are grouped by (dtype, device) -- the reference's dictionary mixes
+    devices: ``gaussian_params`` and ``Tmc`` live on the mapping GPU while ``T_prev_m`` (float64) and
+    ``kf_id`` (int32) stay on the CPU (submap.py:72-84, gaussian_slam.py:225-228) -- and every group is
+    ONE contiguous 1-D block on its source device.  The header records, for every tensor, its path,
+    group, shape and offset inside the group's block."""
+    entries, chunks, groups = [], [], {}
     for path, t in _walk(submap):
-        lst = chunks.setdefault(t.dtype, [])
+        key = (t.dtype, str(t.device))
+        gid = groups.setdefault(key, len(groups))
+        if gid == len(chunks):
+            chunks.append([])
+        lst = chunks[gid]
         off = sum(c.numel() for c in lst)
-        entries.append((path, t.dtype, tuple(t.shape), off))
+        entries.append((path, gid, tuple(t.shape), off))
         lst.append(t.detach().reshape(-1))
-    blocks = {dt: (torch.cat(lst) if len(lst) > 1 else lst[0].clone()) for dt, lst in chunks.items()}
+    blocks = [torch.cat(lst) if len(lst) > 1 else lst[0].clone() for lst in chunks]
     header = {"skeleton": _skeleton(submap), "entries": entries,
-              "sizes": {dt: b.numel() for dt, b in blocks.items()}}
+              "groups": [(dt, dev, blocks[gid].numel()) for (dt, dev), gid in groups.items()]}
     return header, blocks
 
 
-def unpack(header: Dict, blocks: Dict[torch.dtype, torch.Tensor]) -> Dict:
+def unpack(header: Dict, blocks: List[torch.Tensor]) -> Dict:
     import copy
     out = copy.deepcopy(header["skeleton"])
-    for path, dt, shape, off in header["entries"]:
+    for path, gid, shape, off in header["entries"]:
         n = 1
         for s in shape:
             n *= s
-        _set(out, path, blocks[dt][off:off + n].view(shape))
+        _set(out, path, blocks[gid][off:off + n].view(shape))
     return out
 
 
@@ -99,11 +107,13 @@ class SubmapMailbox:
         self._box: Dict[int, Dict] = {}
 
     def put(self, submap: Dict, device) -> None:
-        """Move ``submap`` to ``device`` (one peer copy per dtype) and publish it under its id."""
+        """Move ``submap`` to ``device`` (one copy per (dtype, source device) block) and publish it under its id."""
         check_layout(submap)
         device = torch.device(device)
         header, blocks = pack(submap)
-        moved = {dt: b.to(device, non_blocking=True) for dt, b in blocks.items()}
+        # everything ends up on ``device``, as ``torch.load(path, map_location=device)`` leaves it
+        # (submap.py:28); one copy per (dtype, source device) group
+        moved = [b.to(device, non_blocking=True) for b in blocks]
         if device.type == "cuda":
             # the consumer runs on another thread / stream: hand over only completed copies
             torch.cuda.current_stream(device).synchronize()
@@ -123,14 +133,23 @@ class SubmapMailbox:
             return sorted(self._box)
 
 
+def _wire_device(group=None) -> torch.device:
+    """Where tensors must live to cross the process group: the current CUDA device under NCCL, else CPU."""
+    import torch.distributed as dist
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" \
+        else torch.device("cpu")
+
+
 def send_submap(submap: Dict, dst: int, group=None) -> None:
-    """Rank-to-rank hand-off (parallel loop closure, one submap per GPU)."""
+    """Rank-to-rank hand-off (parallel loop closure, one submap per GPU): a pickled header, then one
+    send per (dtype, source device) block (NCCL P2P over NVLink for the GPU-resident blocks)."""
     import torch.distributed as dist
     check_layout(submap)
     header, blocks = pack(submap)
+    wire = _wire_device(group)
     dist.send_object_list([header], dst=dst, group=group)
-    for dt in sorted(blocks, key=str):
-        dist.send(blocks[dt].contiguous(), dst=dst, group=group)
+    for b in blocks:
+        dist.send(b.to(wire).contiguous(), dst=dst, group=group)
 
 
 def recv_submap(src: int, device, group=None) -> Dict:
@@ -138,11 +157,12 @@ def recv_submap(src: int, device, group=None) -> Dict:
     box = [None]
     dist.recv_object_list(box, src=src, group=group)
     header = box[0]
-    blocks = {}
-    for dt in sorted(header["sizes"], key=str):
-        buf = torch.empty(header["sizes"][dt], dtype=dt, device=device)
+    wire, device = _wire_device(group), torch.device(device)
+    blocks = []
+    for dt, _dev, n in header["groups"]:
+        buf = torch.empty(n, dtype=dt, device=wire)
         dist.recv(buf, src=src, group=group)
-        blocks[dt] = buf
+        blocks.append(buf.to(device))
     return unpack(header, blocks)
 
 

@@ -38,8 +38,8 @@ def assert_same(a, b):
 def test_pack_unpack_roundtrip_and_single_block_per_dtype():
     sm = make_submap()
     header, blocks = handoff.pack(sm)
-    assert set(blocks) == {torch.float32, torch.float64, torch.int64}
-    assert blocks[torch.float32].numel() == 1234 * (3 + 3 + 3 + 4 + 1)
+    assert [(dt, dev) for dt, dev, _ in header["groups"]] == [(torch.float32, "cpu"), (torch.float64, "cpu"), (torch.int64, "cpu")]
+    assert blocks[0].numel() == 1234 * (3 + 3 + 3 + 4 + 1)
     assert_same(handoff.unpack(header, blocks), sm)
 
 
@@ -78,6 +78,42 @@ def _worker(rank, port):
 
 def test_rank_to_rank_gloo():
     mp.spawn(_worker, args=(29577,), nprocs=2, join=True)
+
+
+def like_from_model(sm, dev):
+    """The device mix Submap.from_model really produces (submap.py:72-84): gaussian_params and Tmc on the
+    mapping device, T_prev_m float64 on the CPU (gaussian_slam.py:225-228), kf_id int32 on the CPU."""
+    out = dict(sm)
+    out["gaussian_params"] = {n: t.to(dev) for n, t in sm["gaussian_params"].items()}
+    out["Tmc"] = sm["Tmc"].to(dev)
+    out["kf_id"] = sm["kf_id"].int()
+    return out
+
+
+def test_pack_groups_by_dtype_and_device():
+    sm = like_from_model(make_submap(4), "meta")      # "meta" stands in for the second device on a CPU box
+    groups = {}
+    for _, t in handoff._walk(sm):
+        groups.setdefault((t.dtype, str(t.device)), 0)
+    assert set(groups) == {(torch.float32, "meta"), (torch.float64, "meta"), (torch.float64, "cpu"), (torch.int32, "cpu")}
+    header, blocks = handoff.pack(sm)
+    assert {(dt, dev) for dt, dev, _ in header["groups"]} == set(groups)
+    assert all(b.device.type == dev for b, (_, dev, _) in zip(blocks, header["groups"]))
+
+
+@pytest.mark.gpu
+def test_mailbox_takes_the_mixed_device_dict_of_from_model():
+    """Tmc on the GPU + T_prev_m on the CPU used to hit torch.cat's same-device check."""
+    sm = make_submap(9, P=20_000)
+    src = like_from_model(sm, "cuda:0")
+    dst = f"cuda:{torch.cuda.device_count() - 1}"     # another device when the box has one
+    box = handoff.SubmapMailbox()
+    box.put(src, dst)
+    got = box.get(9, pop=True)
+    assert all(str(t.device) == dst for _, t in handoff._walk(got))
+    ref = dict(sm)
+    ref["kf_id"] = sm["kf_id"].int()
+    assert_same(got, ref)
 
 
 @pytest.mark.gpu
