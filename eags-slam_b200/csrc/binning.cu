@@ -8,14 +8,18 @@
 //   K2 tile_scan   : exclusive scan of the per-tile key counts (counted by preprocess_fwd) ->
 //                    `ranges` (== identifyTileRanges output, (0,0) for empty tiles) + scatter cursors.
 //   K3 duplicate   : (preprocess.cu) scatters (depth_bits << 32 | gaussian) into the tile's bucket.
-//   K4 sort_pack   : one CTA per tile sorts its bucket in shared memory (bitonic network on the 64-bit
-//                    composite; ties on depth fall back to the Gaussian index, which inside one tile
-//                    IS upstream's emission order, so the order equals the stable radix sort's), then
-//                    gathers each splat's attributes once and writes the packed, sorted splat stream
-//                    (48 B records) that blend_fwd / blend_bwd stream with TMA bulk copies.
+//   K4 sort_pack   : one CTA per tile sorts its bucket in shared memory -- an LSD radix sort over the
+//                    depth bits that actually vary inside the tile (8-bit digits, warp-level
+//                    match_any ranking, Gaussian index as payload: 3 passes for a tile spanning
+//                    1..4 m), then orders exact depth ties by Gaussian index, which inside one tile
+//                    IS upstream's emission order, so the result equals upstream's stable radix sort
+//                    of (tile | depth) keys bit for bit -- then gathers each splat's attributes once
+//                    and writes the packed, sorted splat stream (48 B records) that blend_fwd /
+//                    blend_bwd stream with TMA bulk copies.  Tie runs longer than 32 keys (degenerate
+//                    inputs) fall back to a bitonic network on the 64-bit (depth | index) composite.
 //                    Tiles with more than EAGS_SORT_SMALL_CAP keys go to a persistent 1024-thread
-//                    variant with 128 KB of shared memory; beyond EAGS_SORT_BIG_CAP the same network
-//                    runs in global memory (correct, slow, never seen in SLAM submaps).
+//                    variant with 128 KB of shared memory; beyond EAGS_SORT_BIG_CAP the bitonic
+//                    network runs in global memory (correct, slow, never seen in SLAM submaps).
 #include "kernels.h"
 
 namespace {
@@ -222,6 +226,155 @@ __device__ __forceinline__ void load_and_sort(u64* s, const u64* __restrict__ sr
     bitonic_sort_hybrid<THREADS>(s, npad);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Per-tile LSD radix sort (the default): keys = depth bits, payload = Gaussian index.
+// ------------------------------------------------------------------------------------------------
+// Arrangement: warp w owns positions [w * wspan, (w + 1) * wspan) of the list, lane l holds position
+// w * wspan + 32 r + l in round r ("warp-striped"), so list order == (warp, round, lane) order and a
+// stable rank is  base[digit] + (keys with that digit in earlier warps) + (earlier ones of this warp).
+// The last term comes from __match_any_sync: the lanes of a round that share a digit see each other's
+// mask, the lowest one advances the warp's running per-digit counter.  One pass = 3 block barriers.
+// Only the bits in which the tile's depths differ are sorted: digits of (depth_bits - min).
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX_DIGITS = 1 << RADIX_BITS;
+constexpr int TIE_RUN_MAX = 32;   // longer runs of exactly equal depth go to the bitonic fallback
+
+template <int THREADS>
+struct RadixSmem {
+    unsigned cnt[(THREADS / 32) * RADIX_DIGITS];   // [warp][digit]
+    unsigned base[RADIX_DIGITS];
+    unsigned wmin[32], wmax[32], wtot[8];
+};
+
+// Returns true when s_key / s_val[0 .. n) hold the list ordered by (depth bits, index); false when a
+// tie run was too long for the in-place fix-up (caller sorts the 64-bit composite instead).
+template <int THREADS, int ITEMS>
+__device__ __forceinline__ bool radix_sort_tile(unsigned* s_key, unsigned* s_val, RadixSmem<THREADS>& sm,
+                                                const u64* __restrict__ src, int n) {
+    constexpr int NW = THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const int wspan = (((n + NW - 1) / NW) + 31) & ~31;
+    const int rounds = wspan >> 5;                       // <= ITEMS because n <= THREADS * ITEMS
+    const int p0 = warp * wspan + lane;
+    unsigned key[ITEMS], val[ITEMS];
+    unsigned kmin = 0xffffffffu, kmax = 0u;
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++) {
+        key[r] = 0u; val[r] = 0u;
+        const int p = p0 + 32 * r;
+        if (r < rounds && p < n) {
+            const u64 k = src[p];
+            key[r] = (unsigned)(k >> 32);
+            val[r] = (unsigned)k;
+            kmin = min(kmin, key[r]);
+            kmax = max(kmax, key[r]);
+        }
+    }
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if (lane == 0) { sm.wmin[warp] = kmin; sm.wmax[warp] = kmax; }
+    __syncthreads();
+    kmin = __reduce_min_sync(0xffffffffu, lane < NW ? sm.wmin[lane] : 0xffffffffu);
+    kmax = __reduce_max_sync(0xffffffffu, lane < NW ? sm.wmax[lane] : 0u);
+    const unsigned range = kmax - kmin;
+    const int nbits = range ? 32 - __clz(range) : 0;
+    if (nbits == 0) {                                    // one depth value: only the tie order is left
+#pragma unroll
+        for (int r = 0; r < ITEMS; r++) {
+            const int p = p0 + 32 * r;
+            if (r < rounds && p < n) { s_key[p] = key[r]; s_val[p] = val[r]; }
+        }
+        __syncthreads();
+    }
+    for (int shift = 0; shift < nbits; shift += RADIX_BITS) {
+        unsigned* cw = sm.cnt + warp * RADIX_DIGITS;
+#pragma unroll
+        for (int d = 0; d < RADIX_DIGITS; d += 32) cw[d + lane] = 0u;
+        __syncwarp();
+        unsigned short lrank[ITEMS];
+#pragma unroll
+        for (int r = 0; r < ITEMS; r++) {
+            lrank[r] = 0;
+            if (r < rounds) {                            // warp-uniform
+                const bool valid = p0 + 32 * r < n;
+                const unsigned d = valid ? ((key[r] - kmin) >> shift) & (RADIX_DIGITS - 1) : RADIX_DIGITS;
+                const unsigned peers = __match_any_sync(0xffffffffu, d);
+                const unsigned below = __popc(peers & lt);
+                const unsigned prev = valid ? cw[d] : 0u;
+                __syncwarp();
+                if (valid && below == 0) cw[d] = prev + __popc(peers);
+                __syncwarp();
+                lrank[r] = (unsigned short)(prev + below);
+            }
+        }
+        __syncthreads();
+        // digit bases: exclusive scan over (digit major, warp minor)
+        unsigned total = 0;
+        if (tid < RADIX_DIGITS) {
+#pragma unroll 4
+            for (int w = 0; w < NW; w++) {
+                const unsigned c = sm.cnt[w * RADIX_DIGITS + tid];
+                sm.cnt[w * RADIX_DIGITS + tid] = total;
+                total += c;
+            }
+        }
+        unsigned incl = total;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (tid < RADIX_DIGITS && lane == 31) sm.wtot[warp] = incl;
+        __syncthreads();
+        if (tid < RADIX_DIGITS) {
+            unsigned b = incl - total;
+            for (int w = 0; w < warp; w++) b += sm.wtot[w];
+            sm.base[tid] = b;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < ITEMS; r++) {
+            if (r < rounds && p0 + 32 * r < n) {
+                const unsigned d = ((key[r] - kmin) >> shift) & (RADIX_DIGITS - 1);
+                const unsigned pos = sm.base[d] + cw[d] + lrank[r];
+                s_key[pos] = key[r];
+                s_val[pos] = val[r];
+            }
+        }
+        __syncthreads();
+        if (shift + RADIX_BITS < nbits) {
+#pragma unroll
+            for (int r = 0; r < ITEMS; r++) {
+                const int p = p0 + 32 * r;
+                if (r < rounds && p < n) { key[r] = s_key[p]; val[r] = s_val[p]; }
+            }
+        }
+    }
+    // exact depth ties: the radix sort is stable w.r.t. the bucket order, which is arbitrary (atomic
+    // slots); upstream's order inside a tie is the emission order == ascending Gaussian index
+    bool bad = false;
+    for (int k = tid; k < n - 1; k += THREADS)
+        if (s_key[k] == s_key[k + 1] && s_val[k] > s_val[k + 1]) bad = true;
+    if (!__syncthreads_or(bad)) return true;
+    bool too_long = false;
+    for (int k = tid; k < n - 1; k += THREADS) {
+        const unsigned kk = s_key[k];
+        if ((k == 0 || s_key[k - 1] != kk) && s_key[k + 1] == kk) {   // k starts a run
+            int len = 2;
+            while (k + len < n && len <= TIE_RUN_MAX && s_key[k + len] == kk) len++;
+            if (len > TIE_RUN_MAX) { too_long = true; continue; }
+            for (int i = 1; i < len; i++) {                           // insertion sort of the indices
+                const unsigned v = s_val[k + i];
+                int j = i - 1;
+                while (j >= 0 && s_val[k + j] > v) { s_val[k + j + 1] = s_val[k + j]; j--; }
+                s_val[k + j + 1] = v;
+            }
+        }
+    }
+    return !__syncthreads_or(too_long);
+}
+
 struct PackArgs {
     const float2* xy;
     const float4* conic_opacity;
@@ -231,12 +384,12 @@ struct PackArgs {
     unsigned long long* keys;   // nullable
 };
 
-template <int THREADS>
-__device__ __forceinline__ void pack_sorted(const unsigned long long* s, int n, unsigned start,
-                                            unsigned tile, const PackArgs& a) {
+// entry k of the sorted list is (depth_bits, gaussian) = get(k)
+template <int THREADS, typename Get>
+__device__ __forceinline__ void pack_sorted(Get get, int n, unsigned start, unsigned tile, const PackArgs& a) {
     for (int k = threadIdx.x; k < n; k += THREADS) {
-        const unsigned long long key = s[k];
-        const unsigned idx = (unsigned)(key & 0xffffffffull);
+        const uint2 e = get(k);
+        const unsigned idx = e.y;
         const float2 xy = a.xy[idx];
         const float4 co = a.conic_opacity[idx];
         const float4 cd = a.rgbd[idx];
@@ -247,17 +400,41 @@ __device__ __forceinline__ void pack_sorted(const unsigned long long* s, int n, 
         a.records[3 * o + 0] = make_float4(xy.x, xy.y, __uint_as_float(idx), cd.w);
         a.records[3 * o + 1] = make_float4(-0.5f * L * co.x, -L * co.y, -0.5f * L * co.z, co.w);
         a.records[3 * o + 2] = make_float4(cd.x, cd.y, cd.z, __log2f(255.f * co.w));
-        if (a.keys) a.keys[o] = ((unsigned long long)tile << 32) | (key >> 32);
+        if (a.keys) a.keys[o] = ((unsigned long long)tile << 32) | e.x;
+    }
+}
+
+// sort (radix, bitonic fallback) + pack of one tile whose list fits THREADS * ITEMS keys of shared memory
+template <int THREADS, int ITEMS>
+__device__ __forceinline__ void sort_pack_tile(u64* s_keys, RadixSmem<THREADS>& sm, const u64* __restrict__ src,
+                                               int n, unsigned start, unsigned tile, int use_radix,
+                                               const PackArgs& a) {
+    unsigned* s_key = reinterpret_cast<unsigned*>(s_keys);
+    unsigned* s_val = s_key + THREADS * ITEMS;
+    if (use_radix && radix_sort_tile<THREADS, ITEMS>(s_key, s_val, sm, src, n)) {
+        pack_sorted<THREADS>([=](int k) { return make_uint2(s_key[k], s_val[k]); }, n, start, tile, a);
+    } else {
+        __syncthreads();
+        load_and_sort<THREADS>(s_keys, src, n);
+        pack_sorted<THREADS>([=](int k) { const u64 e = s_keys[k]; return make_uint2((unsigned)(e >> 32), (unsigned)e); },
+                             n, start, tile, a);
     }
 }
 
 #ifndef SORT_THREADS
 #define SORT_THREADS 256
 #endif
-__global__ void __launch_bounds__(SORT_THREADS)
+#ifndef SORT_MIN_CTAS
+#define SORT_MIN_CTAS 4
+#endif
+constexpr int SORT_ITEMS = EAGS_SORT_SMALL_CAP / SORT_THREADS;
+constexpr int BIG_ITEMS = EAGS_SORT_BIG_CAP / 1024;
+
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_CTAS)
 sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ unsorted,
-                       long long capacity, unsigned tile_cap, PackArgs a) {
-    __shared__ unsigned long long s_keys[EAGS_SORT_SMALL_CAP];
+                       long long capacity, unsigned tile_cap, int use_radix, PackArgs a) {
+    __shared__ __align__(16) unsigned long long s_keys[EAGS_SORT_SMALL_CAP];
+    __shared__ RadixSmem<SORT_THREADS> s_radix;
     if (img.ctrl->num_rendered > (unsigned long long)capacity) return;
     if (tile_cap && img.ctrl->bucket_overflow) return;
     const unsigned tile = blockIdx.x;
@@ -265,14 +442,16 @@ sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ uns
     const int n = (int)(rg.y - rg.x);
     if (n <= 0 || n > EAGS_SORT_SMALL_CAP) return;
     // bucketed forward: the tile's keys sit in its fixed-stride bucket, not at the scanned offset
-    load_and_sort<SORT_THREADS>(s_keys, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
-    pack_sorted<SORT_THREADS>(s_keys, n, rg.x, tile, a);
+    sort_pack_tile<SORT_THREADS, SORT_ITEMS>(s_keys, s_radix,
+                                             unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n, rg.x,
+                                             tile, use_radix, a);
 }
 
 __global__ void __launch_bounds__(1024)
 sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, long long capacity,
-                     unsigned tile_cap, PackArgs a) {
-    extern __shared__ unsigned long long s_big[];
+                     unsigned tile_cap, int use_radix, PackArgs a) {
+    extern __shared__ __align__(16) unsigned long long s_big[];   // keys, then the radix counters
+    RadixSmem<1024>& s_radix = *reinterpret_cast<RadixSmem<1024>*>(s_big + EAGS_SORT_BIG_CAP);
     if (img.ctrl->num_rendered > (unsigned long long)capacity) return;
     if (tile_cap && img.ctrl->bucket_overflow) return;
     const unsigned n_big = img.ctrl->n_big;
@@ -280,14 +459,14 @@ sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, l
         const unsigned tile = img.big_list[b];
         const uint2 rg = img.ranges[tile];
         const int n = (int)(rg.y - rg.x);
+        unsigned long long* g = unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x);
+        __syncthreads();   // previous tile's pack has finished reading s_big
         if (n <= EAGS_SORT_BIG_CAP) {
-            __syncthreads();   // previous tile's pack has finished reading s_big
-            load_and_sort<1024>(s_big, unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n);
-            pack_sorted<1024>(s_big, n, rg.x, tile, a);
+            sort_pack_tile<1024, BIG_ITEMS>(s_big, s_radix, g, n, rg.x, tile, use_radix, a);
         } else {
-            unsigned long long* g = unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x);   // in place, in global memory
-            bitonic_sort_generic<1024>(g, n);
-            pack_sorted<1024>(g, n, rg.x, tile, a);
+            bitonic_sort_generic<1024>(g, n);   // in place, in global memory
+            pack_sorted<1024>([=](int k) { const u64 e = g[k]; return make_uint2((unsigned)(e >> 32), (unsigned)e); },
+                              n, rg.x, tile, a);
         }
     }
 }
@@ -299,14 +478,15 @@ int launch_tile_scan(ImagePtrs img, cudaStream_t s) {
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, cudaStream_t s) {
+int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
+                     cudaStream_t s) {
     PackArgs a;
     a.xy = geom.xy; a.conic_opacity = geom.conic_opacity; a.rgbd = geom.rgbd;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
-    sort_pack_small_kernel<<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
+    sort_pack_small_kernel<<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
-    static const size_t big_smem = (size_t)EAGS_SORT_BIG_CAP * sizeof(unsigned long long);
-    // opt in to 128 KB of dynamic shared memory (per device; cheap, idempotent)
+    static const size_t big_smem = (size_t)EAGS_SORT_BIG_CAP * sizeof(unsigned long long) + sizeof(RadixSmem<1024>);
+    // opt in to > 48 KB of dynamic shared memory (per device; cheap, idempotent)
     cudaError_t e = cudaFuncSetAttribute(sort_pack_big_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)big_smem);
     if (e != cudaSuccess) return -1;
@@ -314,6 +494,6 @@ int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned til
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = img.G < sms ? img.G : sms;
-    sort_pack_big_kernel<<<grid, 1024, big_smem, s>>>(img, bin.unsorted, bin.capacity, tile_cap, a);
+    sort_pack_big_kernel<<<grid, 1024, big_smem, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
     return cudaPeekAtLastError() == cudaSuccess ? 2 : -1;
 }

@@ -125,6 +125,7 @@ constexpr int FWD_ROUNDS = FWD_BATCH / 32;
 struct FwdArgs {
     int W, H, gx, n_units;
     const EagsCtrl* ctrl;
+    EagsCtrl* stats;
     unsigned* work;
     long long capacity;
     unsigned tile_cap;
@@ -140,7 +141,9 @@ struct FwdArgs {
     uint32_t* tile_max;
 };
 
-template <bool VARIANT_B, bool TMA>
+// STATS ("kernel_stats" option, bench.py only): count the (block, splat) iterations of pass 2 and the
+// (pixel, splat) pairs that were blended into the control block.
+template <bool VARIANT_B, bool TMA, bool STATS>
 __global__ void __launch_bounds__(BLK)
 blend_fwd_kernel(FwdArgs a) {
     __shared__ __align__(128) float4 s_rec[FWD_STAGES][FWD_BATCH * 3];
@@ -158,6 +161,7 @@ blend_fwd_kernel(FwdArgs a) {
     }
     if (VARIANT_B) s_touched[tid] = 0;   // FWD_BATCH == BLK
     unsigned it = 0;   // batches issued to the mbarrier ring so far (identical in every thread)
+    unsigned st_iters = 0, st_pairs = 0;
 
     for (;;) {
         if (tid == 0) s_unit = (int)atomicAdd(a.work, 1u);
@@ -229,9 +233,11 @@ blend_fwd_kernel(FwdArgs a) {
                         const float dx = r0.x - pxf, dy = r0.y - pyf;
                         const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
                         const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
+                        if (STATS) st_iters += (lane == 0);
                         if (power2 > 0.f || alpha < 1.0f / 255.0f) continue;
                         const float test_T = T * (1.f - alpha);
                         if (test_T < 0.0001f) { T = -fabsf(T); continue; }
+                        if (STATS) st_pairs++;
                         const float4 r2 = rec[3 * j + 2];
                         const float w = alpha * T;
                         C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
@@ -288,6 +294,14 @@ blend_fwd_kernel(FwdArgs a) {
         const unsigned m = __reduce_max_sync(FULL, last);
         if (lane == 0 && m) atomicMax(&a.tile_max[tile], m);   // tile_scan zeroed it
     }
+    if (STATS) {
+        st_iters = __reduce_add_sync(FULL, st_iters);
+        st_pairs = __reduce_add_sync(FULL, st_pairs);
+        if (lane == 0) {
+            atomicAdd(&a.stats->stat_fwd_warp_iters, (unsigned long long)st_iters);
+            atomicAdd(&a.stats->stat_fwd_lane_pairs, (unsigned long long)st_pairs);
+        }
+    }
 }
 
 // ================================================================================================
@@ -312,6 +326,7 @@ struct BwdArgs {
     const float* dL_ddepth;
     const float* dL_dthird;   // nullable
     float4* grad_acc;         // [P][3]
+    unsigned long long* stats;   // STATS: {warp iterations, lane pairs}
 };
 
 // Transposed accumulation ("phase 2").  Phase 1 runs pixel-per-lane and leaves, for each of up to 16
@@ -375,7 +390,7 @@ __device__ __forceinline__ void flush_slots(const float2 (*gw)[SLOT_STRIDE], con
 #ifndef BWD_MIN_CTAS
 #define BWD_MIN_CTAS 7
 #endif
-template <bool TMA>
+template <bool TMA, bool STATS>
 __global__ void __launch_bounds__(BLK, BWD_MIN_CTAS)
 blend_bwd_kernel(BwdArgs a) {
     __shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 3];
@@ -391,6 +406,7 @@ blend_bwd_kernel(BwdArgs a) {
         mbar_fence_init();
     }
     unsigned it = 0;
+    unsigned st_iters = 0, st_pairs = 0;
     const float ddelx_dx = 0.5f * (float)a.W, ddely_dy = 0.5f * (float)a.H;
 
     for (;;) {
@@ -481,6 +497,7 @@ blend_bwd_kernel(BwdArgs a) {
                         const float alpha = fminf(0.99f, r1.w * G);
                         const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
                                             (alpha >= 1.0f / 255.0f);
+                        if (STATS) { st_iters += (lane == 0); st_pairs += active; }
                         if (!__any_sync(FULL, active)) continue;   // warp-uniform
                         float gG = 0.f, w = 0.f;
                         if (active) {
@@ -522,6 +539,14 @@ blend_bwd_kernel(BwdArgs a) {
             flush_slots(s_gw[warp], s_pix[warp], s_meta[warp], nslot, lane, rx0, ry0, ddelx_dx, ddely_dy,
                         a.grad_acc);
     }
+    if (STATS) {
+        st_iters = __reduce_add_sync(FULL, st_iters);
+        st_pairs = __reduce_add_sync(FULL, st_pairs);
+        if (lane == 0) {
+            atomicAdd(&a.stats[0], (unsigned long long)st_iters);
+            atomicAdd(&a.stats[1], (unsigned long long)st_pairs);
+        }
+    }
 }
 
 // resident CTAs of a persistent kernel on the current device (occupancy x SM count), cached
@@ -538,27 +563,30 @@ int persistent_grid(K kernel, int units) {
 }  // namespace
 
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
-                     int use_tma, unsigned tile_cap, cudaStream_t s) {
+                     int use_tma, int stats, unsigned tile_cap, cudaStream_t s) {
     FwdArgs a;
     a.tile_cap = tile_cap;
     a.W = v.image_width; a.H = v.image_height; a.gx = img.gx; a.n_units = img.G * UNITS_PER_TILE;
-    a.ctrl = img.ctrl; a.work = &img.ctrl->work_fwd;
+    a.ctrl = img.ctrl; a.stats = img.ctrl; a.work = &img.ctrl->work_fwd;
     a.capacity = bin.capacity; a.ranges = img.ranges; a.records = bin.records;
     a.bg = v.bg; a.out_color = out.color; a.out_depth = out.depth; a.out_third = out.third;
     a.n_touched = out.n_touched; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.tile_max = img.tile_max;
-    if (v.variant == EAGS_VARIANT_B) {
-        if (use_tma) blend_fwd_kernel<true, true><<<persistent_grid(blend_fwd_kernel<true, true>, a.n_units), BLK, 0, s>>>(a);
-        else blend_fwd_kernel<true, false><<<persistent_grid(blend_fwd_kernel<true, false>, a.n_units), BLK, 0, s>>>(a);
+#define EAGS_FWD(B, T, S) blend_fwd_kernel<B, T, S><<<persistent_grid(blend_fwd_kernel<B, T, S>, a.n_units), BLK, 0, s>>>(a)
+    const bool vb = v.variant == EAGS_VARIANT_B;
+    if (stats) {
+        if (vb) { if (use_tma) EAGS_FWD(true, true, true); else EAGS_FWD(true, false, true); }
+        else { if (use_tma) EAGS_FWD(false, true, true); else EAGS_FWD(false, false, true); }
     } else {
-        if (use_tma) blend_fwd_kernel<false, true><<<persistent_grid(blend_fwd_kernel<false, true>, a.n_units), BLK, 0, s>>>(a);
-        else blend_fwd_kernel<false, false><<<persistent_grid(blend_fwd_kernel<false, false>, a.n_units), BLK, 0, s>>>(a);
+        if (vb) { if (use_tma) EAGS_FWD(true, true, false); else EAGS_FWD(true, false, false); }
+        else { if (use_tma) EAGS_FWD(false, true, false); else EAGS_FWD(false, false, false); }
     }
+#undef EAGS_FWD
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
 int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
-                     float* grad_acc, unsigned* work, int use_tma, cudaStream_t s) {
+                     float* grad_acc, unsigned* work, unsigned long long* stats, int use_tma, cudaStream_t s) {
     BwdArgs a;
     a.W = v.image_width; a.H = v.image_height; a.gx = img.gx; a.n_units = img.G * UNITS_PER_TILE;
     a.work = work;
@@ -566,7 +594,10 @@ int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const Ea
     a.final_T = img.final_T; a.n_contrib = img.n_contrib; a.bg = v.bg;
     a.dL_dcolor = gin.dL_dcolor; a.dL_ddepth = gin.dL_ddepth; a.dL_dthird = gin.dL_dthird;
     a.grad_acc = (float4*)grad_acc;
-    if (use_tma) blend_bwd_kernel<true><<<persistent_grid(blend_bwd_kernel<true>, a.n_units), BLK, 0, s>>>(a);
-    else blend_bwd_kernel<false><<<persistent_grid(blend_bwd_kernel<false>, a.n_units), BLK, 0, s>>>(a);
+    a.stats = stats;
+#define EAGS_BWD(T, S) blend_bwd_kernel<T, S><<<persistent_grid(blend_bwd_kernel<T, S>, a.n_units), BLK, 0, s>>>(a)
+    if (stats) { if (use_tma) EAGS_BWD(true, true); else EAGS_BWD(false, true); }
+    else { if (use_tma) EAGS_BWD(true, false); else EAGS_BWD(false, false); }
+#undef EAGS_BWD
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }

@@ -12,6 +12,9 @@ namespace {
 
 thread_local char g_err[512] = "";
 std::atomic<int> g_opt_tma{1};
+std::atomic<int> g_opt_agg{1};
+std::atomic<int> g_opt_radix{1};
+std::atomic<int> g_opt_stats{0};
 std::atomic<unsigned long long> g_launches{0};
 
 // Optional per-kernel timing ("kernel_timing" option): CUDA events recorded on the caller's stream
@@ -87,15 +90,22 @@ size_t eags_binning_state_bytes(int64_t capacity, int32_t with_keys) {
     return binning_layout(capacity, with_keys).total;
 }
 size_t eags_backward_scratch_bytes(int32_t P) { return scratch_layout(P < 0 ? 0 : P).total; }
+size_t eags_backward_stats_offset(int32_t P) { return scratch_layout(P < 0 ? 0 : P).pose + EAGS_SCRATCH_STATS_OFF; }
 
 int eags_set_option(const char* name, int32_t value) {
     if (name && !strcmp(name, "tma")) { g_opt_tma.store(value ? 1 : 0); return 0; }
     if (name && !strcmp(name, "kernel_timing")) { g_opt_timing.store(value ? 1 : 0); return 0; }
+    if (name && !strcmp(name, "preprocess_agg")) { g_opt_agg.store(value ? 1 : 0); return 0; }
+    if (name && !strcmp(name, "radix_sort")) { g_opt_radix.store(value ? 1 : 0); return 0; }
+    if (name && !strcmp(name, "kernel_stats")) { g_opt_stats.store(value ? 1 : 0); return 0; }
     return fail(EAGS_ERR_INVALID, "eags_set_option: unknown option");
 }
 int eags_get_option(const char* name, int32_t* value) {
     if (name && value && !strcmp(name, "tma")) { *value = g_opt_tma.load(); return 0; }
     if (name && value && !strcmp(name, "kernel_timing")) { *value = g_opt_timing.load(); return 0; }
+    if (name && value && !strcmp(name, "preprocess_agg")) { *value = g_opt_agg.load(); return 0; }
+    if (name && value && !strcmp(name, "radix_sort")) { *value = g_opt_radix.load(); return 0; }
+    if (name && value && !strcmp(name, "kernel_stats")) { *value = g_opt_stats.load(); return 0; }
     return fail(EAGS_ERR_INVALID, "eags_get_option: unknown option");
 }
 
@@ -137,7 +147,7 @@ static int forward_geom_impl(const EagsView* view, const EagsGaussians* g, void*
     if (tile_cap > 0) bucket = binning_ptrs(binning_state, capacity, with_keys, (int64_t)IL.G * tile_cap).unsorted;
     // ctrl + tile_count are contiguous: one memset node
     CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4 * EAGS_CTR_STRIDE, s), "memset(ctrl)");
-    CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, bucket, (unsigned)tile_cap, s), "preprocess_fwd");
+    CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, bucket, (unsigned)tile_cap, g_opt_agg.load(), s), "preprocess_fwd");
     CHECK_LAUNCH(launch_tile_scan(img, s), "tile_scan");
     if (ctrl_pinned)
         CHECK_CUDA(cudaMemcpyAsync(ctrl_pinned, img.ctrl, ctrl_bytes, cudaMemcpyDeviceToHost, s), "memcpy(ctrl)");
@@ -160,8 +170,8 @@ static int forward_render_impl(const EagsView* view, const EagsGaussians* g, con
     if (out->n_touched && g->P > 0)
         CHECK_CUDA(cudaMemsetAsync(out->n_touched, 0, (size_t)g->P * 4, s), "memset(n_touched)");
     if (tile_cap == 0) CHECK_LAUNCH(launch_duplicate(*view, g->P, radii, geom, img, bin, s), "duplicate");
-    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, (unsigned)tile_cap, s), "sort_pack");
-    CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), (unsigned)tile_cap, s), "blend_fwd");
+    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, (unsigned)tile_cap, g_opt_radix.load(), s), "sort_pack");
+    CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), g_opt_stats.load(), (unsigned)tile_cap, s), "blend_fwd");
     return 0;
 }
 
@@ -255,7 +265,9 @@ int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int
     float* grad_acc = (float*)((char*)scratch + SL.grad_acc);
     double* pose_acc = (double*)((char*)scratch + SL.pose);
     CHECK_CUDA(cudaMemsetAsync(scratch, 0, SL.pose + 256, s), "memset(scratch)");
-    CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, (unsigned*)((char*)scratch + SL.pose + 128), g_opt_tma.load(), s), "blend_bwd");
+    CHECK_LAUNCH(launch_blend_bwd(*view, img, bin, *gin, grad_acc, (unsigned*)((char*)scratch + SL.pose + EAGS_SCRATCH_WORK_OFF),
+                                  g_opt_stats.load() ? (unsigned long long*)((char*)scratch + SL.pose + EAGS_SCRATCH_STATS_OFF) : nullptr,
+                                  g_opt_tma.load(), s), "blend_bwd");
     CHECK_LAUNCH(launch_preprocess_bwd(*view, *g, radii, geom, grad_acc, *gout, pose_acc, route, s), "preprocess_bwd");
     return 0;
 }

@@ -71,15 +71,17 @@ static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys, i
 // Every launcher returns the number of kernels it launched (>= 0) or -1 after a launch error
 // (cudaGetLastError is left set for the caller).
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
-                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, cudaStream_t s);
+                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, int aggregate,
+                          cudaStream_t s);
 int launch_tile_scan(ImagePtrs img, cudaStream_t s);
 int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs geom, ImagePtrs img,
                      BinningPtrs bin, cudaStream_t s);
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, cudaStream_t s);
+int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
+                     cudaStream_t s);
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
-                     int use_tma, unsigned tile_cap, cudaStream_t s);
+                     int use_tma, int stats, unsigned tile_cap, cudaStream_t s);
 int launch_blend_bwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImageGrads& gin,
-                     float* grad_acc, unsigned* work, int use_tma, cudaStream_t s);
+                     float* grad_acc, unsigned* work, unsigned long long* stats, int use_tma, cudaStream_t s);
 int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32_t* radii,
                           GeomPtrs geom, const float* grad_acc, const EagsInputGrads& gout,
                           double* pose_acc, const EagsPeerRoute* route, cudaStream_t s);

@@ -46,7 +46,11 @@ struct EagsCtrl {
     unsigned int work_fwd;
     unsigned int max_tile;             // largest per-tile key count (tile_scan): sizes the next call's buckets
     unsigned int bucket_overflow;      // bucketed forward: some tile outgrew its bucket, nothing was rendered
-    unsigned int pad[7];
+    unsigned int pad0;
+    // "kernel_stats" option only (bench.py's executed-work roofline): work blend_fwd really did
+    unsigned long long stat_fwd_warp_iters;   // (8x4 block, splat) pairs that survived the cull
+    unsigned long long stat_fwd_lane_pairs;   // (pixel, splat) pairs that were blended
+    unsigned long long pad1;
 };
 static_assert(sizeof(EagsCtrl) == 64, "ctrl block is 64 bytes");
 
@@ -109,6 +113,9 @@ static inline BinningLayout binning_layout(int64_t cap, int with_keys, int64_t b
 }
 
 // backward scratch: grad_acc float[P][12] | pose accumulators double[16] | work queue u32 (at pose + 128)
+//                   | "kernel_stats": blend_bwd warp iterations, lane pairs (2 x u64 at pose + 144)
+#define EAGS_SCRATCH_WORK_OFF 128
+#define EAGS_SCRATCH_STATS_OFF 144
 struct ScratchLayout {
     size_t grad_acc, pose, total;
 };

@@ -20,6 +20,75 @@ namespace {
 // ------------------------------------------------------------------------------------------------
 // K1
 // ------------------------------------------------------------------------------------------------
+// Geometry of one Gaussian up to its tile rectangle; false = culled.  CamPtr is
+// `const float*` (registers) or `const volatile float*` (shared memory, re-read at every use): the
+// arithmetic and its order are the same, so the results are bit-identical either way.
+struct Splat {
+    float p[3];
+    float px, py, depth;
+    float4 con;
+    int r, x0, y0, x1, y1;
+};
+
+template <typename CamPtr>
+__device__ __forceinline__ bool project_one(const PreArgs& a, CamPtr V, CamPtr F, int i, Splat& s) {
+    s.p[0] = a.means3D[(size_t)3 * i]; s.p[1] = a.means3D[(size_t)3 * i + 1]; s.p[2] = a.means3D[(size_t)3 * i + 2];
+    float pv[3];
+    pv[0] = V[0] * s.p[0] + V[4] * s.p[1] + V[8] * s.p[2] + V[12];
+    pv[1] = V[1] * s.p[0] + V[5] * s.p[1] + V[9] * s.p[2] + V[13];
+    pv[2] = V[2] * s.p[0] + V[6] * s.p[1] + V[10] * s.p[2] + V[14];
+    if (pv[2] <= 0.2f) return false;
+    float hx = F[0] * s.p[0] + F[4] * s.p[1] + F[8] * s.p[2] + F[12];
+    float hy = F[1] * s.p[0] + F[5] * s.p[1] + F[9] * s.p[2] + F[13];
+    float hw = F[3] * s.p[0] + F[7] * s.p[1] + F[11] * s.p[2] + F[15];
+    float pw = 1.0f / (hw + 0.0000001f);
+    float ppx = hx * pw, ppy = hy * pw;
+    float c6[6];
+    load_cov6(a, i, c6);
+    float fx = (float)a.W / (2.f * a.tanfovx);
+    float fy = (float)a.H / (2.f * a.tanfovy);
+    Ewa e;
+    ewa_project_lean(V, fx, fy, a.tanfovx, a.tanfovy, pv, c6, e);
+    float ca = e.cov[0], cb = e.cov[1], cc = e.cov[2];
+    float det = ca * cc - cb * cb;
+    if (det == 0.0f) return false;
+    float det_inv = 1.f / det;
+    float mid = 0.5f * (ca + cc);
+    float sq = sqrtf(fmaxf(0.1f, mid * mid - det));
+    float lambda1 = mid + sq, lambda2 = mid - sq;
+    float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+    s.px = ((ppx + 1.0f) * (float)a.W - 1.0f) * 0.5f;
+    s.py = ((ppy + 1.0f) * (float)a.H - 1.0f) * 0.5f;
+    s.r = (int)my_radius;
+    tile_rect(s.px, s.py, s.r, a.gx, a.gy, s.x0, s.y0, s.x1, s.y1);
+    if ((s.x1 - s.x0) * (s.y1 - s.y0) == 0) return false;
+    s.con = make_float4(cc * det_inv, -cb * det_inv, ca * det_inv, 0.f);
+    s.depth = pv[2];
+    return true;
+}
+
+// colour + the per-Gaussian geom records of a surviving Gaussian
+__device__ __forceinline__ void emit_one(const PreArgs& a, const GeomPtrs& geom, int i, Splat& s,
+                                         const float* sh_row) {
+    float rgb[3];
+    unsigned clamped = 0;
+    if (a.colors_precomp) {
+        rgb[0] = a.colors_precomp[(size_t)3 * i];
+        rgb[1] = a.colors_precomp[(size_t)3 * i + 1];
+        rgb[2] = a.colors_precomp[(size_t)3 * i + 2];
+    } else {
+        float cp[3] = {__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)};
+        sh_to_rgb(a.degree, s.p, cp, sh_row, rgb, clamped);
+    }
+    geom.xy[i] = make_float2(s.px, s.py);
+    s.con.w = a.opacities[i];
+    geom.conic_opacity[i] = s.con;
+    geom.rgbd[i] = make_float4(rgb[0], rgb[1], rgb[2], s.depth);
+    geom.clamped[i] = (uint8_t)clamped;
+}
+
+// One thread per Gaussian, one global atomic per (Gaussian, tile): the general kernel (wide SH rows,
+// images with more tiles than the aggregating kernel's shared-memory histogram holds).
 template <bool WIDE>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
@@ -30,48 +99,12 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     unsigned my_tiles = 0;
     // phase A: geometry up to the tile rectangle; `alive` = survives every cull
     bool alive = false;
-    float p[3] = {0.f, 0.f, 0.f};
-    float px = 0.f, py = 0.f, depth = 0.f;
-    float4 con = make_float4(0.f, 0.f, 0.f, 0.f);
-    int r = 0, x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    Splat sp;
+    sp.r = 0; sp.x0 = sp.y0 = sp.x1 = sp.y1 = 0; sp.depth = 0.f;
     if (i < a.P) {
         float V[16], F[16];
         load_cam(a, V, F);
-        do {
-            p[0] = a.means3D[(size_t)3 * i]; p[1] = a.means3D[(size_t)3 * i + 1]; p[2] = a.means3D[(size_t)3 * i + 2];
-            float pv[3];
-            pv[0] = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
-            pv[1] = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
-            pv[2] = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
-            if (pv[2] <= 0.2f) break;
-            float hx = F[0] * p[0] + F[4] * p[1] + F[8] * p[2] + F[12];
-            float hy = F[1] * p[0] + F[5] * p[1] + F[9] * p[2] + F[13];
-            float hw = F[3] * p[0] + F[7] * p[1] + F[11] * p[2] + F[15];
-            float pw = 1.0f / (hw + 0.0000001f);
-            float ppx = hx * pw, ppy = hy * pw;
-            float c6[6];
-            load_cov6(a, i, c6);
-            float fx = (float)a.W / (2.f * a.tanfovx);
-            float fy = (float)a.H / (2.f * a.tanfovy);
-            Ewa e;
-            ewa_project(V, fx, fy, a.tanfovx, a.tanfovy, pv, c6, e);
-            float ca = e.cov[0], cb = e.cov[1], cc = e.cov[2];
-            float det = ca * cc - cb * cb;
-            if (det == 0.0f) break;
-            float det_inv = 1.f / det;
-            float mid = 0.5f * (ca + cc);
-            float sq = sqrtf(fmaxf(0.1f, mid * mid - det));
-            float lambda1 = mid + sq, lambda2 = mid - sq;
-            float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
-            px = ((ppx + 1.0f) * (float)a.W - 1.0f) * 0.5f;
-            py = ((ppy + 1.0f) * (float)a.H - 1.0f) * 0.5f;
-            r = (int)my_radius;
-            tile_rect(px, py, r, a.gx, a.gy, x0, y0, x1, y1);
-            if ((x1 - x0) * (y1 - y0) == 0) break;
-            con = make_float4(cc * det_inv, -cb * det_inv, ca * det_inv, 0.f);
-            depth = pv[2];
-            alive = true;
-        } while (0);
+        alive = project_one(a, (const float*)V, (const float*)F, i, sp);
     }
     // phase B (wide SH rows): the warp fetches the rows of its surviving Gaussians, coalesced
     const float* sh_row = nullptr;
@@ -89,22 +122,9 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     if (i < a.P) {
         int r_out = 0;
         if (alive) {
-            float rgb[3];
-            unsigned clamped = 0;
-            if (a.colors_precomp) {
-                rgb[0] = a.colors_precomp[(size_t)3 * i];
-                rgb[1] = a.colors_precomp[(size_t)3 * i + 1];
-                rgb[2] = a.colors_precomp[(size_t)3 * i + 2];
-            } else {
-                float cp[3] = {__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)};
-                sh_to_rgb(a.degree, p, cp, sh_row, rgb, clamped);
-            }
-            geom.xy[i] = make_float2(px, py);
-            con.w = a.opacities[i];
-            geom.conic_opacity[i] = con;
-            geom.rgbd[i] = make_float4(rgb[0], rgb[1], rgb[2], depth);
-            geom.clamped[i] = (uint8_t)clamped;
-            r_out = r;
+            emit_one(a, geom, i, sp, sh_row);
+            r_out = sp.r;
+            const int x0 = sp.x0, y0 = sp.y0, x1 = sp.x1, y1 = sp.y1;
             my_tiles = (unsigned)((x1 - x0) * (y1 - y0));
             if (bucket == nullptr) {
                 // exact path: per-tile key counts only (no-return RED atomics spread over G addresses);
@@ -115,7 +135,7 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                 // bucketed path: the returning atomic IS the slot inside the tile's fixed-stride bucket,
                 // so the key is scattered here and there is no second pass over the Gaussians.  Four
                 // atomics are kept in flight before the dependent stores.
-                const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
+                const unsigned long long key = ((unsigned long long)__float_as_uint(sp.depth) << 32) | (unsigned)i;
                 const int n = (int)my_tiles;
                 int x = x0, y = y0;
                 bool over = false;
@@ -150,6 +170,98 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     if ((threadIdx.x & 31) == 0 && s) atomicAdd(&ctrl->num_rendered, (unsigned long long)s);
 }
 
+// CTA-aggregated K1 (the default for narrow SH rows).  The one-atomic-per-key kernel above is bound by
+// the L2 atomic transaction rate (~47 G atomics/s: 886 K keys = 19 us at c2, whatever else the kernel
+// does).  Here one CTA per SM owns a contiguous span of P / #SM Gaussians and
+//   phase 1  runs the per-Gaussian preprocess and counts the span's keys per tile in a SHARED-memory
+//            histogram (shared atomics),
+//   phase 2  reserves, with ONE global atomic per (CTA, touched tile), a run of that many slots in the
+//            tile's bucket (or, on the exact path, adds the count with a RED) and turns the histogram
+//            entry into the run's cursor,
+//   phase 3  re-derives each Gaussian's tile rectangle from the records it wrote in phase 1 (L2-resident,
+//            same thread) and scatters its keys at cursor++ (shared atomics again).
+// Global atomics per view drop from K to (#CTAs x tiles a span touches): 5x fewer at c2 for Gaussians in
+// random order, ~#tiles-per-span fewer when the submap is stored in image order (SLAM seeds Gaussians
+// from keyframe pixels, so neighbours in memory share tiles).  The order inside a bucket is arbitrary
+// either way: sort_pack orders by (depth, index).
+constexpr int AGG_THREADS = 1024;
+constexpr int AGG_MAX_TILES = 24 * 1024;   // 96 KB histogram
+
+__global__ void __launch_bounds__(AGG_THREADS, 1)
+preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
+                          uint32_t* __restrict__ tile_count, EagsCtrl* __restrict__ ctrl,
+                          unsigned long long* __restrict__ bucket, unsigned tile_cap, int span) {
+    extern __shared__ unsigned s_hist[];   // G counters, then the two camera matrices (32 floats)
+    __shared__ unsigned s_sum[AGG_THREADS / 32];
+    const int G = a.gx * a.gy, tid = threadIdx.x;
+    float* s_cam = reinterpret_cast<float*>(s_hist + G);
+    for (int t = tid; t < G; t += AGG_THREADS) s_hist[t] = 0u;
+    if (tid < 32) s_cam[tid] = tid < 16 ? __ldg(a.view + tid) : __ldg(a.proj + tid - 16);
+    __syncthreads();
+    const volatile float* V = s_cam;
+    const volatile float* F = s_cam + 16;
+    const int begin = blockIdx.x * span, end = min(a.P, begin + span);
+    unsigned my_total = 0;
+    // ---- phase 1
+    for (int i = begin + tid; i < end; i += AGG_THREADS) {
+        Splat sp;
+        unsigned my_tiles = 0;
+        int r_out = 0;
+        if (project_one(a, V, F, i, sp)) {
+            emit_one(a, geom, i, sp, a.colors_precomp ? nullptr : a.shs + (size_t)i * a.M * 3);
+            r_out = sp.r;
+            my_tiles = (unsigned)((sp.x1 - sp.x0) * (sp.y1 - sp.y0));
+            for (int y = sp.y0; y < sp.y1; y++)
+                for (int x = sp.x0; x < sp.x1; x++) atomicAdd(&s_hist[y * a.gx + x], 1u);
+        }
+        radii[i] = r_out;
+        geom.tiles_touched[i] = my_tiles;
+        my_total += my_tiles;
+    }
+    __syncthreads();
+    // ---- phase 2
+    for (int t = tid; t < G; t += AGG_THREADS) {
+        const unsigned c = s_hist[t];
+        if (c) {
+            if (bucket) s_hist[t] = atomicAdd(&tile_count[(size_t)t * EAGS_CTR_STRIDE], c);
+            else atomicAdd(&tile_count[(size_t)t * EAGS_CTR_STRIDE], c);
+        }
+    }
+    // ---- phase 3
+    if (bucket) {
+        __syncthreads();
+        bool over = false;
+        for (int i = begin + tid; i < end; i += AGG_THREADS) {
+            const int r = radii[i];
+            if (r <= 0) continue;
+            const float2 xy = geom.xy[i];
+            const float depth = geom.rgbd[i].w;
+            int x0, y0, x1, y1;
+            tile_rect(xy.x, xy.y, r, a.gx, a.gy, x0, y0, x1, y1);
+            const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
+            for (int y = y0; y < y1; y++)
+                for (int x = x0; x < x1; x++) {
+                    const unsigned t = (unsigned)(y * a.gx + x);
+                    const unsigned slot = atomicAdd(&s_hist[t], 1u);
+                    if (slot < tile_cap) bucket[(size_t)t * tile_cap + slot] = key;
+                    else over = true;
+                }
+        }
+        if (over) ctrl->bucket_overflow = 1u;   // the caller re-issues on the exact path
+    }
+    // K = sum tiles_touched: one atomic per CTA
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_total += __shfl_xor_sync(0xffffffffu, my_total, o);
+    if ((tid & 31) == 0) s_sum[tid >> 5] = my_total;
+    __syncthreads();
+    if (tid < 32) {
+        unsigned v = s_sum[tid];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (tid == 0 && v) atomicAdd(&ctrl->num_rendered, (unsigned long long)v);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K3
 // ------------------------------------------------------------------------------------------------
@@ -178,16 +290,38 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, GeomP
 
 }  // namespace
 
+// "preprocess_agg" option (c_api.cu): 1 = CTA-aggregated K1 where it applies (default), 0 = always the
+// one-atomic-per-key kernel (A/B measurements, parity tests of both)
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
-                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, cudaStream_t s) {
+                          int32_t* radii, unsigned long long* bucket, unsigned tile_cap, int aggregate,
+                          cudaStream_t s) {
     if (g.P <= 0) return 0;
     PreArgs a = make_args(v, g);
-    const int grid = (g.P + PRE_THREADS - 1) / PRE_THREADS;
     if (wide_sh(a)) {
+        const int grid = (g.P + PRE_THREADS - 1) / PRE_THREADS;
         if (!allow_wide_smem(preprocess_fwd_kernel<true>)) return -1;
         preprocess_fwd_kernel<true><<<grid, PRE_THREADS, wide_sh_smem(a), s>>>(
             a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
+    } else if (aggregate && img.G <= AGG_MAX_TILES) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        // one CTA per SM; spans are multiples of the CTA width so every pass of a CTA is fully coalesced
+        int span = (g.P + sms - 1) / sms;
+        span = ((span + AGG_THREADS - 1) / AGG_THREADS) * AGG_THREADS;
+        const int grid = (g.P + span - 1) / span;
+        const size_t smem = ((size_t)img.G + 32) * sizeof(unsigned);
+        static bool opted[64] = {};
+        if (smem > 48 * 1024 && dev >= 0 && dev < 64 && !opted[dev]) {
+            if (cudaFuncSetAttribute(preprocess_fwd_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(((size_t)AGG_MAX_TILES + 32) * sizeof(unsigned))) != cudaSuccess)
+                return -1;
+            opted[dev] = true;
+        }
+        preprocess_fwd_agg_kernel<<<grid, AGG_THREADS, smem, s>>>(
+            a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap, span);
     } else {
+        const int grid = (g.P + PRE_THREADS - 1) / PRE_THREADS;
         preprocess_fwd_kernel<false><<<grid, PRE_THREADS, 0, s>>>(
             a, geom, radii, img.tile_count, img.ctrl, tile_cap ? bucket : nullptr, tile_cap);
     }

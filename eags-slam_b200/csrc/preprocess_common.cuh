@@ -123,7 +123,8 @@ __device__ __forceinline__ void ewa_project(const float* V, float fx, float fy, 
 }
 
 // K8 variant: R_w2c is NOT copied into e.Wm (the caller re-reads it from shared memory at every use)
-__device__ __forceinline__ void ewa_project_lean(const volatile float* V, float fx, float fy, float tanfovx,
+template <typename CamPtr>
+__device__ __forceinline__ void ewa_project_lean(CamPtr V, float fx, float fy, float tanfovx,
                                             float tanfovy, const float pview[3], const float c6[6],
                                             Ewa& e) {
     float limx = 1.3f * tanfovx, limy = 1.3f * tanfovy;

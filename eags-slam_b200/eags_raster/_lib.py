@@ -74,6 +74,7 @@ SIGNATURES = {
     "eags_image_state_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "eags_binning_state_bytes": (C.c_size_t, [C.c_int64, C.c_int32]),
     "eags_backward_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "eags_backward_stats_offset": (C.c_size_t, [C.c_int32]),
     "eags_set_option": (C.c_int, [C.c_char_p, C.c_int32]),
     "eags_get_option": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32)]),
     "eags_kernel_times": (C.c_int, [C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]),

@@ -38,6 +38,23 @@ _bucketed = os.environ.get("EAGS_BUCKETED", "1") != "0"   # optimistic mode: sca
 _MAX_BUCKET_SLOTS = 1 << 28                               # 2 GiB of keys; beyond that use the exact path
 
 
+_kernel_stats = False
+
+
+def enable_kernel_stats(on: bool) -> None:
+    """Measurement only (bench.py's executed-work roofline): the blend kernels count the (8x4 block, splat)
+    iterations they walk after the cull and the (pixel, splat) pairs they blend.  Read them with
+    :func:`forward_stats` and from ``rasterize_backward(...)["stats"]``."""
+    global _kernel_stats
+    _kernel_stats = bool(on)
+    _lib.set_option("kernel_stats", int(on))
+
+
+def forward_stats(state) -> dict:
+    ctrl = state_array(state, "ctrl").view(torch.int64)
+    return {"warp_iters": int(ctrl[5]), "lane_pairs": int(ctrl[6])}
+
+
 def set_bucketed(on: bool) -> None:
     """Optimistic mode only: let stage 1 scatter the keys into per-tile buckets sized from the
     previous frames' largest tile (no duplicate kernel); off = always the exact path."""
@@ -451,6 +468,10 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                 # returns the sum over all views of all ranks (and the chain rule above them runs once)
                 route.end_pass()
                 out.update(means3D=None, scales=None, rotations=None, opacities=None)
+        if _kernel_stats:
+            off = int(lib.eags_backward_stats_offset(P))
+            st64 = scratch[off:off + 16].view(torch.int64)
+            out["stats"] = {"warp_iters": int(st64[0]), "lane_pairs": int(st64[1])}
         del keep
     return out
 

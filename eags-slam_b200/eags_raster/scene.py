@@ -22,6 +22,12 @@ WORKLOADS = {
     # 2x the 876x584 intrinsics of reference configs/scannetpp/281bc17764.yaml:9-14
     "c4": (1752, 1168, 625.584, 626.960, 876.0, 584.0, 1_500_000),
     "c5": (640, 480, 517.306408, 516.469215, 318.643040, 255.313989, 300_000),
+    # the shapes the reference's variant-A call sites really pass (dataset size AFTER the
+    # crop of src/entities/datasets.py:34-39, principal point shifted by the crop)
+    "tum_crop": (540, 380, 517.306408, 516.469215, 318.643040 - 50, 255.313989 - 50, 200_000),     # crop_edge 50
+    "scannet_crop": (616, 456, 577.590698, 578.729797, 318.905426 - 12, 242.683609 - 12, 200_000),  # scannet.yaml:49-56
+    "scannetpp": (876, 584, 312.79197434640764, 313.48022477591036, 438.0, 292.0, 300_000),        # 281bc17764.yaml:9-14
+    "replica": (1200, 680, 600.0, 600.0, 599.5, 339.5, 300_000),                                    # replica.yaml:49-55
     # test-only shapes (ragged: 70x52 is not a multiple of the 16x16 tile)
     "tiny": (64, 48, 51.7306408, 51.6469215, 31.8643040, 25.5313989, 300),
     "ragged": (70, 52, 56.0, 55.0, 33.3, 27.1, 400),
@@ -79,10 +85,16 @@ def keyframe_views(workload: str, n_views: int = 8):
 
 def make_scene(workload: str = "c2", P: int | None = None, seed: int = 0, M: int = 1,
                device="cpu", outside: float = 0.05, behind: float = 0.02,
-               scale_range=(0.7, 2.5)) -> Dict[str, torch.Tensor]:
+               scale_range=(0.7, 2.5), order: str = "random") -> Dict[str, torch.Tensor]:
     """Synthetic Gaussians per SURVEY 8(d): pixels uniform in the image (+5 % outside up to
     1.5x the frustum, 2 % behind the camera), depth U(1,4) m, per-axis scale (z/fx)*U(0.7,2.5),
-    random unit quaternions, opacity sigmoid(N(0,1.5^2)), SH-DC U(-1.7,1.7)."""
+    random unit quaternions, opacity sigmoid(N(0,1.5^2)), SH-DC U(-1.7,1.7).
+
+    ``order`` is the storage order of the same Gaussians: "random" (neighbours in memory
+    land anywhere in the image -- the adversarial case for tile binning), "raster" (by seeding pixel,
+    row-major: how the reference seeds a keyframe's Gaussians from its pixels, mapper.py:225-260 /
+    gaussian_model.py:586-592) or "tile" (by 16x16 tile of the seeding pixel, see
+    :func:`tile_order`)."""
     W, H, fx, fy, cx, cy, P0 = WORKLOADS[workload]
     P = int(P0 if P is None else P)
     g = torch.Generator().manual_seed(int(seed))
@@ -111,9 +123,37 @@ def make_scene(workload: str = "c2", P: int | None = None, seed: int = 0, M: int
         shs[:, 1:, :] = 0.1 * torch.randn(P, M - 1, 3, generator=g)
     gt_color = torch.rand(3, H, W, generator=g)
     gt_depth = 1.0 + 3.0 * torch.rand(1, H, W, generator=g)
-    out = dict(means3D=means3D, scales=scales, rotations=rotations, opacities=opacities, shs=shs,
-               gt_color=gt_color, gt_depth=gt_depth)
+    out = dict(means3D=means3D, scales=scales, rotations=rotations, opacities=opacities, shs=shs)
+    if order != "random":
+        ui, vi = u.clamp(0, W - 1).long(), v.clamp(0, H - 1).long()
+        if order == "raster":
+            key = vi * W + ui
+        elif order == "tile":
+            key = ((vi // 16) * ((W + 15) // 16) + ui // 16) * 256 + (vi % 16) * 16 + ui % 16
+        else:
+            raise ValueError("order must be 'random', 'raster' or 'tile'")
+        perm = torch.argsort(key, stable=True)
+        out = {k: t[perm] for k, t in out.items()}
+    out.update(gt_color=gt_color, gt_depth=gt_depth)
     return {k: t.to(torch.float32).contiguous().to(device) for k, t in out.items()}
+
+
+def tile_order(means3D: torch.Tensor, cam: "Camera") -> torch.Tensor:
+    """Permutation that stores a submap's Gaussians by the 16x16 tile their mean projects to in ``cam``
+    (Gaussians outside the image or behind the camera last).  Applying it to every per-Gaussian tensor
+    (and the optimiser state) changes no rendered value -- the rasterizer's output order is (depth, index)
+    per tile and ties are measure-zero -- but lets preprocess_fwd's CTA-level aggregation reserve whole
+    runs of a tile's bucket with one atomic (csrc/preprocess.cu)."""
+    dev = means3D.device
+    w2c = cam.w2c.to(dev)
+    pc = means3D @ w2c[:3, :3].T + w2c[:3, 3]
+    z = pc[:, 2].clamp_min(1e-6)
+    ui = (pc[:, 0] / z * cam.fx + cam.cx - 0.5).floor().long()
+    vi = (pc[:, 1] / z * cam.fy + cam.cy - 0.5).floor().long()
+    inside = (pc[:, 2] > 0.2) & (ui >= 0) & (ui < cam.W) & (vi >= 0) & (vi < cam.H)
+    gx = (cam.W + 15) // 16
+    key = torch.where(inside, (vi // 16) * gx + ui // 16, torch.full_like(ui, 1 << 40))
+    return torch.argsort(key, stable=True)
 
 
 def workload_camera(workload: str, w2c=None) -> Camera:

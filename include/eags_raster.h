@@ -115,6 +115,9 @@ size_t eags_geom_state_bytes(int32_t P);
 size_t eags_image_state_bytes(int32_t width, int32_t height);
 size_t eags_binning_state_bytes(int64_t capacity, int32_t with_keys);
 size_t eags_backward_scratch_bytes(int32_t P);
+/* byte offset, inside the backward scratch, of two uint64 counters the "kernel_stats" option makes
+ * blend_bwd fill: (8x4 pixel block, splat) pairs walked, (pixel, splat) pairs with a gradient */
+size_t eags_backward_stats_offset(int32_t P);
 
 /* Forward, stage 1: per-Gaussian preprocess (cull, EWA projection, conic, radius, tile rectangle,
  * SH->RGB), per-tile counts and the tile scan.  Writes `radii` (P) and, when
@@ -145,7 +148,10 @@ typedef struct EagsForwardStatus {
     uint32_t n_big, work_sort, work_fwd;
     uint32_t max_tile;        /* largest per-tile key count of this view                  */
     uint32_t bucket_overflow; /* != 0: a tile outgrew tile_cap                            */
-    uint32_t pad[7];
+    uint32_t pad0;
+    uint64_t stat_fwd_warp_iters; /* "kernel_stats" option: (8x4 pixel block, splat) pairs blend_fwd walked */
+    uint64_t stat_fwd_lane_pairs; /*                        (pixel, splat) pairs blend_fwd blended          */
+    uint64_t pad1;
 } EagsForwardStatus;
 size_t eags_binning_state_bytes_bucketed(int64_t capacity, int32_t with_keys, int32_t width,
                                          int32_t height, int32_t tile_cap);
@@ -294,6 +300,13 @@ int eags_state_view(const char* what, int32_t P, int32_t width, int32_t height, 
 /* Tuning knobs for A/B measurements (process-wide, read at launch time):
  *   "tma"      1 (default): blend kernels stage splat batches with cp.async.bulk + mbarrier;
  *              0: plain cooperative loads.                                                     */
+/*   "preprocess_agg" 1 (default): CTA-aggregated preprocess_fwd (shared-memory tile histogram, one global
+ *              atomic per (CTA, touched tile)); 0: one global atomic per (Gaussian, tile) key.
+ *   "radix_sort" 1 (default): per-tile LSD radix sort on the varying depth bits; 0: bitonic network on the
+ *              64-bit (depth | index) composite.  Both settings give bit-identical results.
+ *   "kernel_stats" 1: the blend kernels count the work they really executed (post-cull) into
+ *              EagsForwardStatus.stat_* / the backward scratch (bench.py's executed-work roofline);
+ *              default 0 (the counting instantiations are never launched).                       */
 /*   "kernel_timing" 1: record CUDA events on the caller's stream around every kernel launcher;
  *              read them with eags_kernel_times().  Default 0 (no events are ever recorded).    */
 int eags_set_option(const char* name, int32_t value);

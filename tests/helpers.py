@@ -34,6 +34,39 @@ def assert_close_rel(a, b, rtol, atol_frac, what=""):
                            f"{np.abs(a - b).max():.3e} (max|ref| {np.abs(b).max():.3e})")
 
 
+def assert_pixels_rel(a, b, rtol=1e-5, floor=1e-3, what=""):
+    """TRUE elementwise relative error: |a-b| <= rtol * |b| wherever |b| > floor (no absolute slack
+    borrowed from the brightest pixel), and |a-b| <= rtol * floor below it.  Returns the worst relative
+    error seen above the floor (for the test log)."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    big = np.abs(b) > floor
+    err = np.abs(a - b)
+    rel = np.where(big, err / np.maximum(np.abs(b), floor), 0.0)
+    bad = (big & (rel > rtol)) | (~big & (err > rtol * floor))
+    assert not bad.any(), (f"{what}: {bad.sum()} / {bad.size} elements exceed {rtol:g} relative "
+                           f"(worst {rel.max():.3e} above the {floor:g} floor, worst abs below it "
+                           f"{(err * ~big).max():.3e})")
+    return float(rel.max())
+
+
+def assert_rows_rel(a, b, rtol=1e-3, row_floor=1e-3, what=""):
+    """Row-wise gradient check: every row (one Gaussian) whose reference max-norm exceeds
+    ``row_floor * max|b|`` must agree to ``rtol`` relative to ITS OWN max-norm; smaller rows to
+    ``rtol * row_floor * max|b|`` absolute.  Returns the worst per-row relative error."""
+    a = np.asarray(a, dtype=np.float64).reshape(len(a), -1)
+    b = np.asarray(b, dtype=np.float64).reshape(len(b), -1)
+    gmax = max(np.abs(b).max(), 1e-30)
+    rown = np.abs(b).max(axis=1)
+    err = np.abs(a - b).max(axis=1)
+    big = rown > row_floor * gmax
+    rel = np.where(big, err / np.maximum(rown, 1e-30), 0.0)
+    bad = (big & (rel > rtol)) | (~big & (err > rtol * row_floor * gmax))
+    assert not bad.any(), (f"{what}: {bad.sum()} / {len(bad)} rows exceed {rtol:g} (worst row-relative "
+                           f"{rel.max():.3e}; {big.sum()} rows above the floor)")
+    return float(rel.max())
+
+
 # ---- GPU-side helpers (the CUDA path under test, called through the C ABI binding) ----------------
 class Settings:
     """Duck-typed GaussianRasterizationSettings built from a scene.Camera (device tensors)."""

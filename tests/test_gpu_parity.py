@@ -60,7 +60,10 @@ def _check_forward(o, out, state, variant):
     np.testing.assert_array_equal(np.stack([(cl >> c) & 1 for c in range(3)], 1), o["clamped"][vis])
     # ---- images ----
     ok = nonfragile(o)
-    assert ok.mean() > 0.98
+    # fragile pixels: 0.006 % (c1) .. 0.04 % (c2) of a full-size image; the 3 000-pixel test images may
+    # hold a handful.  They differ by one blended splat (the 1/255 alpha cut or the T < 1e-4 stop falls on
+    # the other side of the threshold in the other implementation's rounding).
+    assert ok.mean() >= (0.999 if ok.size >= 100_000 else 0.99), f"fragile fraction {1 - ok.mean():.4%}"
     nc = _np(state_array(state, "n_contrib")).view(np.uint32)
     np.testing.assert_array_equal(nc[ok], o["n_contrib"][ok])
     assert_close_rel(_np(color)[:, ok], o["color"][:, ok], 1e-5, RTOL_IMG, "color")
