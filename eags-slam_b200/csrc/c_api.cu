@@ -240,6 +240,22 @@ int eags_peer_reduce(const EagsPeerRoute* route, uint32_t epoch, float scale, in
     return 0;
 }
 
+int eags_peer_adam_step(const EagsPeerRoute* route, const EagsPeerAdam* opt, uint32_t epoch, float scale,
+                        int32_t wait, void* stream) {
+    if (!route || !route_ok(route, route->P) || route->P < 0)
+        return fail(EAGS_ERR_INVALID, "eags_peer_adam_step: bad route");
+    if (!opt || !opt->m || !opt->v || !opt->step || !(opt->beta1 >= 0.f && opt->beta1 < 1.f) ||
+        !(opt->beta2 >= 0.f && opt->beta2 < 1.f) || !(opt->eps >= 0.f))
+        return fail(EAGS_ERR_INVALID, "eags_peer_adam_step: bad optimiser state");
+    for (int k = 0; k < route->world; k++)
+        if (!opt->params[k] || (reinterpret_cast<uintptr_t>(opt->params[k]) & 15))
+            return fail(EAGS_ERR_INVALID, "eags_peer_adam_step: parameter replicas must be 16-byte aligned");
+    if (route->P == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_peer_adam(*route, *opt, epoch, scale, wait, s), "peer_adam");
+    return 0;
+}
+
 int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
                          const void* geom_state, const void* image_state, const void* binning_state,
                          int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,

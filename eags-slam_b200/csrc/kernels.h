@@ -111,6 +111,8 @@ int launch_radius_has_neighbor(const float* ref, int n_ref, const float* query, 
 // collective.cu
 size_t peer_flags_bytes();
 int launch_peer_reduce(const EagsPeerRoute& r, unsigned epoch, float scale, int wait, cudaStream_t s);
+int launch_peer_adam(const EagsPeerRoute& r, const EagsPeerAdam& o, unsigned epoch, float scale, int wait,
+                     cudaStream_t s);
 
 // ssim.cu
 int launch_ssim_fwd(int C, int H, int W, const float* img1, const float* img2, float* part_abc, double* sum,

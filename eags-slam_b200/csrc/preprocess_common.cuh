@@ -316,19 +316,11 @@ inline bool wide_sh(const PreArgs& a) {
 }
 inline size_t wide_sh_smem(const PreArgs& a) { return (size_t)PRE_THREADS * ((3 * a.M) | 1) * sizeof(float); }
 
-// > 48 KB of dynamic shared memory is an opt-in per kernel and device
+// > 48 KB of dynamic shared memory is an opt-in per kernel and device (idempotent and cheap, so it is
+// simply repeated: a per-type cache would be shared by kernels with the same signature)
 template <typename K>
 bool allow_wide_smem(K kernel) {
-    static bool done[64] = {};
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
-    if (!done[dev]) {
-        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SH_WIDE_SMEM) != cudaSuccess)
-            return false;
-        done[dev] = true;
-    }
-    return true;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SH_WIDE_SMEM) == cudaSuccess;
 }
-
 
 }  // namespace

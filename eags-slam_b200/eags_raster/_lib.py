@@ -100,6 +100,7 @@ SIGNATURES = {
                                        C.POINTER(EagsImageGrads), C.POINTER(EagsInputGrads), C.c_void_p,
                                        C.c_void_p, C.c_void_p]),
     "eags_peer_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_float, C.c_int32, C.c_void_p]),
+    "eags_peer_adam_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int32, C.c_void_p]),
     "eags_image_l1_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "eags_image_l1_forward": (C.c_int, [C.POINTER(EagsImageL1), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_void_p]),
@@ -140,7 +141,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.eags_abi_version() != 1:
+    if lib.eags_abi_version() != 2:
         raise ImportError("libeags_raster.so ABI version mismatch; rebuild it")
     _lib = lib
     return lib

@@ -35,6 +35,16 @@ class EagsPeerRoute(C.Structure):
                 ("flags", C.c_void_p * MAX_PEERS), ("accum", C.c_void_p * 4)]
 
 
+class EagsPeerAdam(C.Structure):
+    _fields_ = [("params", C.c_void_p * MAX_PEERS), ("m", C.c_void_p), ("v", C.c_void_p), ("step", C.c_void_p),
+                ("lr", C.c_float * 4), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+                ("isotropic_weight", C.c_float)]
+
+
+class PeerExchangeError(RuntimeError):
+    """A bounded cross-rank wait expired: a peer never delivered its gradients for some step."""
+
+
 def stride_of(P: int) -> int:
     return (int(P) + 3) & ~3
 
@@ -68,7 +78,9 @@ class PeerGradExchange:
         recv_b, red_b = self.world * self.flat * 4, self.flat * 4
         self._off_reduced = (recv_b + 255) & ~255
         self._off_flags = (self._off_reduced + red_b + 255) & ~255
-        total = self._off_flags + self.flags_bytes
+        # raw parameter replica (PeerAdam: owners store updated parameters straight into every replica)
+        self._off_params = (self._off_flags + self.flags_bytes + 255) & ~255
+        total = self._off_params + red_b
         if self.emulated:
             self._bufs = [torch.zeros(total, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
             bases = [b.data_ptr() for b in self._bufs]
@@ -112,15 +124,42 @@ class PeerGradExchange:
         return {"means3D": flat[0:3 * P].view(P, 3), "scales": flat[3 * s:3 * s + 3 * P].view(P, 3),
                 "rotations": flat[6 * s:6 * s + 4 * P].view(P, 4), "opacities": flat[10 * s:10 * s + P].view(P, 1)}
 
+    def recv_views(self, owner: int, src: int):
+        """dict(means3D, scales, rotations, opacities): views of slot ``src`` inside rank ``owner``'s receive area
+        (emulated worlds only -- tests write known gradients here)."""
+        if not self.emulated:
+            raise RuntimeError("recv_views is for emulate_world exchanges")
+        flat = self._bufs[owner][src * self.flat * 4:(src + 1) * self.flat * 4].view(torch.float32)
+        return self._carve(flat)
+
     def error_flag(self, rank: Optional[int] = None) -> int:
-        """Non-zero (the epoch) if a bounded cross-rank wait expired on this rank."""
+        """Non-zero (the first epoch that failed... sticky maximum) if a bounded cross-rank wait expired on
+        this rank.  Synchronises the host with the device (one 4-byte read)."""
         rank = self.rank if rank is None else rank
         words = self._local_buf(rank)[self._off_flags:self._off_flags + self.flags_bytes].view(torch.int32)
         return int(words[2 * MAX_PEERS + 1])
 
+    def check(self, rank: Optional[int] = None) -> None:
+        """Raise :class:`PeerExchangeError` if any exchange since the last check lost a peer.  The step that
+        failed delivered NaN gradients (``reduce``) or skipped its update (``PeerAdam``) -- never a partial
+        sum -- so the caller can stop, fall back to NCCL, or re-run the step."""
+        e = self.error_flag(rank)
+        if e:
+            raise PeerExchangeError(f"peer gradient exchange: rank {self.rank if rank is None else rank} waited "
+                                    f"30 s for a peer at exchange #{e}; that step's result was discarded")
+
+    def param_views(self, rank: Optional[int] = None):
+        """dict(xyz (P,3), scaling (P,3), rotation (P,4), opacity (P,1)): views of this rank's RAW parameter
+        replica inside the peer-mapped buffer (the segment layout of the gradient buffers)."""
+        rank = self.rank if rank is None else rank
+        flat = self._local_buf(rank)[self._off_params:self._off_params + self.flat * 4].view(torch.float32)
+        s, P = self.stride, self.P
+        return {"xyz": flat[0:3 * P].view(P, 3), "scaling": flat[3 * s:3 * s + 3 * P].view(P, 3),
+                "rotation": flat[6 * s:6 * s + 4 * P].view(P, 4), "opacity": flat[10 * s:10 * s + P].view(P, 1)}
+
     # ---- the routed backward ----------------------------------------------------------------------
     def route(self, scale: float = 1.0, rank: Optional[int] = None, reduce: bool = True, accum=None,
-              local_views: int = 1):
+              local_views: int = 1, optimizer: "Optional[PeerAdam]" = None):
         """Context manager: the next rasterizer backward scatters to the owners and (``reduce``) runs the
         peer reduction with ``scale`` (1 / number of views).  ``rank`` selects the emulated rank.
 
@@ -132,8 +171,13 @@ class PeerGradExchange:
         ``local_views=k`` does that bookkeeping here: the context then expects exactly k rasterizer
         backward passes; the first k-1 run the plain backward, are summed into a buffer of this object and
         hand NO gradient to the four routed inputs; the k-th is routed with that sum added and returns
-        the all-rank result, so the activations above the rasterizer back-propagate once per step."""
-        return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce, accum, local_views)
+        the all-rank result, so the activations above the rasterizer back-propagate once per step.
+
+        ``optimizer`` (:class:`PeerAdam`) -- the routed pass ends with the fused owner-side optimiser step
+        instead of the gradient reduction: NO gradient is returned for the four routed inputs (the raw
+        parameters inside the exchange are updated in place on every replica)."""
+        return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce, accum, local_views,
+                         optimizer)
 
     def _local_sums(self):
         """(sums, scratch): two flat 11 x stride fp32 buffers for ``route(local_views > 1)``, made on first use."""
@@ -173,15 +217,100 @@ class PeerGradExchange:
                                         0 if self.emulated else 1, stream), "eags_peer_reduce")
 
 
+class PeerAdam:
+    """The mapping optimiser of sharded mapping, fused into the gradient exchange (csrc/collective.cu
+    ``peer_adam_kernel``; include/eags_raster.h ``eags_peer_adam_step``).
+
+    Holds the RAW parameters of the reference's ``GaussianModel`` (``_xyz``, ``_scaling`` = log scale,
+    ``_rotation`` = un-normalised quaternion, ``_opacity`` = logit; gaussian_model.py:60-81) inside the
+    exchange's peer-mapped buffer and the Adam moments of the Gaussians THIS rank owns (1 / world of the
+    optimiser state).  ``activated()`` gives the tensors the rasterizer takes; after the step's last
+    backward pass (``exchange.route(..., optimizer=self)``) the owner of each Gaussian sums the ranks'
+    gradients, back-propagates through exp / normalize / sigmoid, adds the isotropic regulariser's gradient
+    (mapper.py:166), takes the Adam step of gaussian_model.py:341-356 and stores the new parameters into every
+    replica.  At world size 1 (or ``emulate_world=1``) this is the reference's single-GPU optimiser step.
+    """
+
+    GROUPS = ("xyz", "scaling", "rotation", "opacity")
+
+    def __init__(self, exchange: PeerGradExchange, lr=None, betas=(0.9, 0.999), eps: float = 1e-15,
+                 isotropic_weight: float = 1.0):
+        # learning rates of src/entities/arguments.py:57-64
+        self.lr = dict(xyz=1e-4, scaling=5e-3, rotation=1e-3, opacity=5e-2)
+        self.lr.update(lr or {})
+        self.ex, self.betas, self.eps, self.isotropic_weight = exchange, betas, float(eps), float(isotropic_weight)
+        ranks = range(exchange.world) if exchange.emulated else [exchange.rank]
+        chunk = owner_chunk(exchange.P, exchange.world)
+        dev = exchange.device
+        self._state = {r: (torch.zeros(11 * chunk, dtype=torch.float32, device=dev),
+                           torch.zeros(11 * chunk, dtype=torch.float32, device=dev),
+                           torch.zeros(1, dtype=torch.int32, device=dev)) for r in ranks}
+        self._structs = {r: self._make_struct(r) for r in ranks}
+
+    def _make_struct(self, rank: int) -> EagsPeerAdam:
+        ex, o = self.ex, EagsPeerAdam()
+        for p in range(ex.world):
+            o.params[p] = ex._bases[p] + ex._off_params
+        m, v, step = self._state[rank]
+        o.m, o.v, o.step = m.data_ptr(), v.data_ptr(), step.data_ptr()
+        for k, name in enumerate(self.GROUPS):
+            o.lr[k] = float(self.lr[name])
+        o.beta1, o.beta2, o.eps, o.isotropic_weight = float(self.betas[0]), float(self.betas[1]), self.eps, self.isotropic_weight
+        return o
+
+    def set_lr(self, **lr) -> None:
+        """e.g. the xyz schedule of gaussian_model.py:326-333."""
+        self.lr.update(lr)
+        for r in self._structs:
+            self._structs[r] = self._make_struct(r)
+
+    def params(self, rank: Optional[int] = None):
+        return self.ex.param_views(rank)
+
+    def load(self, xyz, scaling, rotation, opacity, rank: Optional[int] = None) -> None:
+        """Copy initial raw parameters into the replica (every rank loads the same values) and reset the
+        optimiser state."""
+        pv = self.params(rank)
+        with torch.no_grad():
+            pv["xyz"].copy_(xyz); pv["scaling"].copy_(scaling)
+            pv["rotation"].copy_(rotation); pv["opacity"].copy_(opacity.reshape(-1, 1))
+        ranks = [self.ex.rank if rank is None else rank]
+        for r in ranks:
+            for t in self._state[r]:
+                t.zero_()
+
+    def activated(self, rank: Optional[int] = None):
+        """dict(means3D, scales, rotations, opacities) for the rasterizer (gaussian_model.py:103-122);
+        no autograd graph: the chain rule through the activations is part of the fused step."""
+        pv = self.params(rank)
+        with torch.no_grad():
+            return {"means3D": pv["xyz"], "scales": torch.exp(pv["scaling"]),
+                    "rotations": torch.nn.functional.normalize(pv["rotation"]),
+                    "opacities": torch.sigmoid(pv["opacity"])}
+
+    def steps_taken(self, rank: Optional[int] = None) -> int:
+        return int(self._state[self.ex.rank if rank is None else rank][2])
+
+    def step(self, scale: float = 1.0, rank: Optional[int] = None) -> None:
+        """Launch the fused step on the current stream (normally called by the routed backward)."""
+        lib, ex = _lib.load(), self.ex
+        rank = ex.rank if rank is None else rank
+        stream = torch.cuda.current_stream(ex.device).cuda_stream
+        _lib.check(lib.eags_peer_adam_step(C.byref(ex.route_struct(rank)), C.byref(self._structs[rank]), 0,
+                                           float(scale), 0 if ex.emulated else 1, stream), "eags_peer_adam_step")
+
+
 class _RouteCtx:
     def __init__(self, ex: PeerGradExchange, scale: float, rank: int, reduce: bool, accum=None,
-                 local_views: int = 1):
+                 local_views: int = 1, optimizer: Optional[PeerAdam] = None):
         if local_views < 1:
             raise ValueError("route(local_views=...) must be >= 1")
         if accum is not None and local_views != 1:
             raise ValueError("route(): pass either accum= (caller-owned sums) or local_views= (summed here)")
+        if optimizer is not None and optimizer.ex is not ex:
+            raise ValueError("route(optimizer=...): the optimiser belongs to another exchange")
         self.ex, self.scale, self.rank, self.do_reduce, self.accum = ex, scale, rank, reduce, accum
-        self.local_views, self.passes = int(local_views), 0
+        self.local_views, self.passes, self.optimizer = int(local_views), 0, optimizer
 
     # ---- several views per rank per step (called by rasterize_backward) ---------------------------
     def begin_pass(self) -> bool:

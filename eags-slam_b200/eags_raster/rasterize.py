@@ -455,9 +455,16 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                                                 C.byref(gout), scratch.data_ptr(),
                                                 C.byref(ex.route_struct(route.rank, route.pass_accum())), stream),
                        "eags_backward_routed")
-            if route.do_reduce:
-                ex.reduce(route.scale, route.rank)
-            out.update(ex.reduced_views(route.rank))
+            if route.optimizer is not None:
+                # fused owner-side step: sum, activation backward, regulariser, Adam, parameter all-gather
+                # (eags_raster.peer.PeerAdam); the raw parameters were updated in place on every replica
+                if route.do_reduce:
+                    route.optimizer.step(route.scale, route.rank)
+                out.update(means3D=None, scales=None, rotations=None, opacities=None)
+            else:
+                if route.do_reduce:
+                    ex.reduce(route.scale, route.rank)
+                out.update(ex.reduced_views(route.rank))
         else:
             _lib.check(lib.eags_backward(C.byref(view), C.byref(g), state.radii.data_ptr(),
                                          state.geom.data_ptr(), state.image.data_ptr(),

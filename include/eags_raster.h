@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define EAGS_ABI_VERSION 1
+#define EAGS_ABI_VERSION 2
 
 #define EAGS_VARIANT_A 0 /* third image = alpha = sum_i alpha_i T_i          (gaussian_rasterizer)          */
 #define EAGS_VARIANT_B 1 /* third image = opacity = 1 - T_final, + n_touched (diff_gaussian_rasterization)  */
@@ -188,7 +188,9 @@ int eags_backward(const EagsView* view, const EagsGaussians* g, const int32_t* r
  *   flags[p]   : rank p's signal words, eags_peer_flags_bytes() bytes, zeroed once before first use
  * `epoch` = 0 uses a device-side counter kept in `flags` (valid inside CUDA-graph replays); a non-zero
  * value must increase by one per eags_peer_reduce call (start at 1), identically on all ranks.
- * `wait` = 0 skips the cross-rank waits (single-GPU emulation of several ranks in tests). */
+ * `wait` = 0 skips the cross-rank waits (single-GPU emulation of several ranks in tests).
+ * The cross-rank waits are bounded (30 s of wall time): if a peer never arrives the error word in `flags`
+ * is set (sticky) and the result of that step is poisoned with NaN on every replica -- never a partial sum. */
 #define EAGS_MAX_PEERS 8
 typedef struct EagsPeerRoute {
     int32_t rank, world;
@@ -208,6 +210,37 @@ int eags_backward_routed(const EagsView* view, const EagsGaussians* g, const int
                          int64_t capacity, const EagsImageGrads* gin, const EagsInputGrads* gout,
                          void* scratch, const EagsPeerRoute* route, void* stream);
 int eags_peer_reduce(const EagsPeerRoute* route, uint32_t epoch, float scale, int32_t wait, void* stream);
+
+/* Fused optimiser step of sharded mapping ("owner computes"): replaces eags_peer_reduce + the autograd of
+ * the model's activations + the isotropic regulariser's backward + torch.optim.Adam by ONE kernel per
+ * rank.  After eags_backward_routed scattered the gradient rows, the owner of Gaussian i sums its `world`
+ * slots in rank order (x `scale` = 1 / views), applies the chain rule of the reference's parametrisation
+ * (src/entities/gaussian_model.py:77-81: scaling = exp(raw), rotation = normalize(raw), opacity =
+ * sigmoid(raw), xyz raw), adds `isotropic_weight` x d isotropic_loss / d scaling
+ * (src/entities/losses.py:128-138, mapper.py:166), takes the Adam step of
+ * gaussian_model.py:341-356 (per-group lr, eps 1e-15; torch.optim.Adam semantics, amsgrad off) with moments
+ * that live ONLY on the owner, and stores the new raw parameters into EVERY rank's replica through the peer
+ * mapping (the all-gather moves parameters instead of gradients: same bytes, and replicas hold the owner's
+ * bits by construction).  Barriers, `epoch` and `wait` as eags_peer_reduce.
+ *   params[p] : rank p's raw parameter replica, peer-mapped, 11 x stride floats in the segment layout of
+ *               `reduced` (xyz at 0, log-scale at 3 stride, raw quaternion at 6 stride, logit opacity at
+ *               10 stride); the rasterizer reads xyz from it directly
+ *   m, v      : local, 11 x chunk floats each (plane k of coordinate k: m[k * chunk + (i - first owned)]),
+ *               zeroed by the caller before the first step; chunk = ceil(P / world) rounded up to 4
+ *   step      : local uint32 device counter of optimiser steps taken (zeroed once; read for the bias
+ *               corrections, advanced by the kernel -- valid under CUDA-graph replay)
+ * If a peer never arrives (bounded wait, 30 s) NOTHING is updated and the error word in `flags` is set. */
+typedef struct EagsPeerAdam {
+    float* params[EAGS_MAX_PEERS];
+    float* m;
+    float* v;
+    uint32_t* step;
+    float lr[4]; /* xyz, scaling, rotation, opacity (gaussian_model.py:342-347) */
+    float beta1, beta2, eps;
+    float isotropic_weight; /* 1 in the reference (mapper.py:166-167); 0 disables the term */
+} EagsPeerAdam;
+int eags_peer_adam_step(const EagsPeerRoute* route, const EagsPeerAdam* opt, uint32_t epoch, float scale,
+                        int32_t wait, void* stream);
 
 /* ---- Fused image-space losses ---------------------------------------------
  * The per-iteration losses that bracket the rasterizer in the reference: the tracking loss

@@ -35,7 +35,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_sizes_and_errors():
     from eags_raster import _lib
     lib = _lib.load()
-    assert lib.eags_abi_version() == 1
+    assert lib.eags_abi_version() == 2
     # sizes are monotone, 256-byte granular and cover the documented arrays
     g1, g2 = lib.eags_geom_state_bytes(1000), lib.eags_geom_state_bytes(2000)
     assert g2 > g1 >= 1000 * 45 and g1 % 256 == 0

@@ -69,7 +69,11 @@ def test_full_size_parity(wl, P, M, variant, rot):
     worst = {
         "color": assert_pixels_rel(_np(color)[:, ok], o["color"][:, ok], RTOL_IMG, 1e-3, "color"),
         "depth": assert_pixels_rel(_np(depth)[0][ok], o["depth"][0][ok], RTOL_IMG, 1e-3, "depth"),
-        "third": assert_pixels_rel(_np(third)[0][ok], o["third"][0][ok], RTOL_IMG, 1e-3, "alpha/opacity"),
+        # variant A: alpha = sum alpha_i T_i (a sum of positive terms).  Variant B: opacity = 1 - T_final, a
+        # difference of two O(1) numbers -- one ulp of T = 0.999 is already 6e-5 of an opacity of 1e-3 -- so
+        # it is held to 1e-5 of the larger operand (1), and T itself to 1e-5 relative on the line below
+        "third": assert_pixels_rel(_np(third)[0][ok], o["third"][0][ok], RTOL_IMG, 1e-3 if variant == 0 else 1.0,
+                                   "alpha/opacity"),
         "final_T": assert_pixels_rel(_np(state_array(state, "final_T"))[ok], o["final_T"][ok], RTOL_IMG, 1e-3, "final_T"),
     }
     # ---- gradients of the L1 colour + depth loss of bench.py (+ a dense dL/dalpha for variant A)
