@@ -30,7 +30,7 @@ namespace {
 constexpr int SCAN_THREADS = 1024;
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-tile_scan_kernel(ImagePtrs img) {
+tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
     __shared__ unsigned s_warp[SCAN_THREADS / 32];
     __shared__ unsigned s_carry, s_max;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -80,6 +80,13 @@ tile_scan_kernel(ImagePtrs img) {
     if (tid == 0) {
         img.ctrl->num_scanned = s_carry;
         img.ctrl->max_tile = s_max;
+        if (sticky) {
+            // persistent high-water marks over every forward that was handed this block (CUDA-graph replays:
+            // the owner of the graph looks at it once per frame, an overflow in ANY replay must still show)
+            atomicMax(&sticky->num_rendered, img.ctrl->num_rendered);
+            atomicMax(&sticky->max_tile, s_max);
+            atomicOr(&sticky->bucket_overflow, img.ctrl->bucket_overflow);
+        }
     }
 }
 
@@ -473,8 +480,8 @@ sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, l
 
 }  // namespace
 
-int launch_tile_scan(ImagePtrs img, cudaStream_t s) {
-    tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(img);
+int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s) {
+    tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(img, sticky);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -131,7 +131,7 @@ int eags_kernel_times(int32_t max_spans, const char** names, float* ms) {
 static int forward_geom_impl(const EagsView* view, const EagsGaussians* g, void* geom_state,
                              void* image_state, int32_t* radii, void* ctrl_pinned, size_t ctrl_bytes,
                              void* binning_state, int64_t capacity, int32_t with_keys, int32_t tile_cap,
-                             void* stream) {
+                             void* sticky_dev, void* stream) {
     if (!view_ok(view)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad view settings");
     if (!gauss_ok(view, g)) return fail(EAGS_ERR_INVALID, "eags_forward_geom: bad Gaussian inputs");
     if (!image_state || (g->P > 0 && (!geom_state || !radii)))
@@ -148,9 +148,10 @@ static int forward_geom_impl(const EagsView* view, const EagsGaussians* g, void*
     // ctrl + tile_count are contiguous: one memset node
     CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4 * EAGS_CTR_STRIDE, s), "memset(ctrl)");
     CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, bucket, (unsigned)tile_cap, g_opt_agg.load(), s), "preprocess_fwd");
-    CHECK_LAUNCH(launch_tile_scan(img, s), "tile_scan");
+    CHECK_LAUNCH(launch_tile_scan(img, (EagsCtrl*)sticky_dev, s), "tile_scan");
     if (ctrl_pinned)
-        CHECK_CUDA(cudaMemcpyAsync(ctrl_pinned, img.ctrl, ctrl_bytes, cudaMemcpyDeviceToHost, s), "memcpy(ctrl)");
+        CHECK_CUDA(cudaMemcpyAsync(ctrl_pinned, sticky_dev ? sticky_dev : (void*)img.ctrl, ctrl_bytes,
+                                   cudaMemcpyDeviceToHost, s), "memcpy(ctrl)");
     return 0;
 }
 
@@ -178,7 +179,7 @@ static int forward_render_impl(const EagsView* view, const EagsGaussians* g, con
 int eags_forward_geom(const EagsView* view, const EagsGaussians* g, void* geom_state,
                       void* image_state, int32_t* radii, uint64_t* num_rendered_pinned, void* stream) {
     return forward_geom_impl(view, g, geom_state, image_state, radii, num_rendered_pinned, sizeof(uint64_t),
-                             nullptr, 0, 0, 0, stream);
+                             nullptr, 0, 0, 0, nullptr, stream);
 }
 
 int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
@@ -197,10 +198,10 @@ size_t eags_binning_state_bytes_bucketed(int64_t capacity, int32_t with_keys, in
 int eags_forward_geom_bucketed(const EagsView* view, const EagsGaussians* g, void* geom_state,
                                void* image_state, int32_t* radii, EagsForwardStatus* status_pinned,
                                void* binning_state, int64_t capacity, int32_t with_keys, int32_t tile_cap,
-                               void* stream) {
+                               EagsForwardStatus* sticky_status_dev, void* stream) {
     static_assert(sizeof(EagsForwardStatus) == sizeof(EagsCtrl), "status block mirrors the device control block");
     return forward_geom_impl(view, g, geom_state, image_state, radii, status_pinned, sizeof(EagsCtrl),
-                             binning_state, capacity, with_keys, tile_cap, stream);
+                             binning_state, capacity, with_keys, tile_cap, sticky_status_dev, stream);
 }
 
 int eags_forward_render_bucketed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,

@@ -86,7 +86,7 @@ SIGNATURES = {
     "eags_binning_state_bytes_bucketed": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
     "eags_forward_geom_bucketed": (C.c_int, [C.POINTER(EagsView), C.POINTER(EagsGaussians), C.c_void_p,
                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                                             C.c_int32, C.c_int32, C.c_void_p]),
+                                             C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "eags_forward_render_bucketed": (C.c_int, [C.POINTER(EagsView), C.POINTER(EagsGaussians), C.c_void_p,
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                                C.c_int32, C.POINTER(EagsImages), C.c_void_p]),

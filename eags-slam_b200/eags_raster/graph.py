@@ -7,9 +7,10 @@ the host and one host wait (the key count K), which is what bounds the step once
 :class:`GraphedIteration` runs ``fn`` a few times eagerly (learning the binning capacities), captures
 it ONCE into a CUDA graph and replays it: the same kernels, one launch per iteration.
 
-Safety: a replay cannot grow a buffer.  Every captured forward copies its status block (K, per-tile
-maximum, overflow flag) to pinned memory; :meth:`GraphedIteration.check` (call it whenever the host
-synchronises anyway, e.g. once per frame) raises if a replay outgrew the captured capacity -- its
+Safety: a replay cannot grow a buffer.  Every captured forward folds its status (K, per-tile maximum,
+overflow flag) into a persistent device block (atomicMax / atomicOr: sticky over ALL replays) and copies
+that block to pinned memory; :meth:`GraphedIteration.check` (call it whenever the host synchronises
+anyway, e.g. once per frame) raises if ANY replay since the capture outgrew the captured capacity -- its
 outputs were not rendered -- after raising the capacities so that a re-capture succeeds.
 """
 from __future__ import annotations
@@ -22,16 +23,26 @@ from . import rasterize as rz
 
 
 class _CaptureCtx:
-    def __init__(self, n_slots: int):
-        self.free = [torch.zeros(8, dtype=torch.int64).pin_memory() for _ in range(n_slots)]
-        self.used: List[Tuple[torch.Tensor, int]] = []
+    """Per captured forward: a pinned status block the replay copies into, and a persistent DEVICE block
+    (zeroed here, once, never by the forward) that accumulates K / largest tile with atomicMax and the
+    overflow flag with atomicOr over every replay -- the pinned copy is a copy of THAT block, so check()
+    sees an overflow of any replay since the capture, not just the last one."""
 
-    def take_status(self, cap: int) -> torch.Tensor:
+    def __init__(self, n_slots: int, device):
+        self.free = [torch.zeros(8, dtype=torch.int64).pin_memory() for _ in range(n_slots)]
+        self.sticky = [torch.zeros(8, dtype=torch.int64, device=device) for _ in range(n_slots)]
+        self.used: List[Tuple[torch.Tensor, int]] = []
+        self._keep: List[torch.Tensor] = []
+
+    def take_status(self, cap: int, device) -> Tuple[torch.Tensor, torch.Tensor]:
         if not self.free:
             raise RuntimeError("GraphedIteration: more rasterizer calls in one iteration than max_renders")
-        st = self.free.pop()
+        st, sticky = self.free.pop(), self.sticky.pop()
+        if sticky.device != torch.device(device):
+            raise RuntimeError("GraphedIteration: the captured rasterizer call runs on another device than the graph")
         self.used.append((st, cap))
-        return st
+        self._keep.append(sticky)
+        return st, sticky
 
 
 class GraphedIteration:
@@ -53,7 +64,7 @@ class GraphedIteration:
                 fn()
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
-        self._ctx = _CaptureCtx(max_renders)
+        self._ctx = _CaptureCtx(max_renders, self.device)
         self.graph = torch.cuda.CUDAGraph()
         prev = rz._capture_ctx
         rz._capture_ctx = self._ctx

@@ -337,13 +337,18 @@ class _RouteCtx:
 
     def __enter__(self):
         from . import rasterize
-        self.prev = rasterize._peer_route
-        rasterize._peer_route = self
+        idx = self.ex.device.index
+        self.prev = rasterize._peer_route.get(idx)
+        rasterize._peer_route[idx] = self       # per device: another thread's renders elsewhere are unaffected
         return self
 
     def __exit__(self, *exc):
         from . import rasterize
-        rasterize._peer_route = self.prev
+        idx = self.ex.device.index
+        if self.prev is None:
+            rasterize._peer_route.pop(idx, None)
+        else:
+            rasterize._peer_route[idx] = self.prev
         if exc[0] is None and self.passes not in (0, self.local_views):
             raise RuntimeError(f"route(local_views={self.local_views}) saw {self.passes} backward passes: "
                                "the step's gradients were never exchanged")

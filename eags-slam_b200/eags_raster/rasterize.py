@@ -80,9 +80,13 @@ def reserve_capacity(device, num_keys: int) -> None:
     _capacity[idx] = max(_capacity.get(idx, 0), int(num_keys))
 
 
-_arena = None
-_capture_ctx = None  # set by eags_raster.graph.GraphedIteration while it captures
-_peer_route = None   # set by eags_raster.peer.PeerGradExchange.route() (process-wide, like _arena)
+# Keyed by DEVICE INDEX, not process-wide and not thread-local: autograd runs backward() on its own per-device
+# thread, so a thread-local would never be seen by the backward it is meant for, while a process-wide value
+# would leak into the loop-closure thread that renders on another device (reference src/entities/lc.py:625)
+# while sharded mapping runs on this one.  (A pose-only backward -- registration -- ignores both anyway.)
+_arena = {}          # device index -> dict of target tensors (grad_arena)
+_peer_route = {}     # device index -> _RouteCtx (eags_raster.peer.PeerGradExchange.route())
+_capture_ctx = None  # set by eags_raster.graph.GraphedIteration while it captures (capture is process-exclusive)
 
 
 class grad_arena:
@@ -90,23 +94,27 @@ class grad_arena:
     inputs straight into caller-provided tensors (e.g. slices of one fused all-reduce buffer,
     :class:`eags_raster.sharded.FusedGradBucket`) instead of fresh allocations, so a following
     collective needs no packing.  Valid for ONE backward per activation (a second backward would
-    overwrite the first result) and process-wide (do not run another rasterizer backward concurrently
-    on a second thread while it is active); keys: means3D, scales, rotations, opacities, shs, colors_precomp,
-    cov3D_precomp, means2D."""
+    overwrite the first result).  Applies to backward passes on the DEVICE of the given tensors only, so a
+    second thread rendering on another device (the loop-closure worker) is unaffected; keys: means3D,
+    scales, rotations, opacities, shs, colors_precomp, cov3D_precomp, means2D."""
 
     def __init__(self, **tensors):
         self.tensors = tensors
+        devs = {t.device.index for t in tensors.values() if t is not None and t.is_cuda}
+        if len(devs) != 1:
+            raise ValueError("grad_arena: the target tensors must live on one CUDA device")
+        self.index = devs.pop()
 
     def __enter__(self):
-        # process-wide, not thread-local: autograd runs backward() on its own device thread
-        global _arena
-        self.prev = _arena
-        _arena = self.tensors
+        self.prev = _arena.get(self.index)
+        _arena[self.index] = self.tensors
         return self
 
     def __exit__(self, *exc):
-        global _arena
-        _arena = self.prev
+        if self.prev is None:
+            _arena.pop(self.index, None)
+        else:
+            _arena[self.index] = self.prev
         return False
 
 
@@ -135,6 +143,10 @@ def _f32c(t: torch.Tensor, device) -> torch.Tensor:
     (utils.py:97) every call; the materialised copy is cached per (tensor, version)."""
     if t.dtype == torch.float32 and t.is_contiguous() and t.device == device:
         return t
+    if torch.cuda.is_current_stream_capturing():
+        # CUDA-graph capture: the copy must be a node of the graph (re-done from the source view on every
+        # replay, allocated in the graph's pool) -- never a cached tensor that lives outside it
+        return t.detach().to(device=device, dtype=torch.float32).contiguous()
     key = id(t)
     hit = _cont_cache.get(key)
     if hit is not None:
@@ -143,7 +155,12 @@ def _f32c(t: torch.Tensor, device) -> torch.Tensor:
             return out
     out = t.detach().to(device=device, dtype=torch.float32).contiguous()
     if len(_cont_cache) > 256:
-        _cont_cache.clear()
+        # drop entries whose source tensor is gone; never the whole cache (another thread's kernels may
+        # still be reading a live entry's copy)
+        for k in [k for k, (ref, _, _) in list(_cont_cache.items()) if ref() is None]:
+            _cont_cache.pop(k, None)
+        while len(_cont_cache) > 1024:
+            _cont_cache.pop(next(iter(_cont_cache)), None)
     try:
         _cont_cache[key] = (weakref.ref(t), t._version, out)
     except TypeError:
@@ -161,6 +178,21 @@ def _pinned_slot() -> torch.Tensor:
         slot = torch.zeros(1, dtype=torch.int64).pin_memory()
         _tls.slot = slot
     return slot
+
+
+def _nosync_slot() -> torch.Tensor:
+    """nosync mode: a pinned K slot from a per-thread ring.  cudaHostAlloc synchronises the device, so slots
+    are allocated once and recycled as soon as the forward that owned them is no longer pending."""
+    ring = getattr(_tls, "ring", None)
+    if ring is None:
+        ring = _tls.ring = []
+    busy = {id(p[2]) for p in (getattr(_tls, "pending", None) or [])}
+    for s in ring:
+        if id(s) not in busy:
+            return s
+    s = torch.zeros(1, dtype=torch.int64).pin_memory()
+    ring.append(s)
+    return s
 
 
 def _pinned_status() -> torch.Tensor:
@@ -281,11 +313,11 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
             tile_cap = _tile_cap.get(key, 0) if _bucketed else 0
             if tile_cap * G > _MAX_BUCKET_SLOTS:
                 tile_cap = 0
-            status = cap_ctx.take_status(cap)
+            status, sticky = cap_ctx.take_status(cap, device)
             binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
             _lib.check(lib.eags_forward_geom_bucketed(
                 C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
-                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, stream),
+                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, sticky.data_ptr(), stream),
                 "eags_forward_geom_bucketed")
             _lib.check(lib.eags_forward_render_bucketed(
                 C.byref(view), C.byref(g), radii.data_ptr(), geom.data_ptr(), image.data_ptr(),
@@ -307,7 +339,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
             binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
             _lib.check(lib.eags_forward_geom_bucketed(
                 C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
-                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, stream),
+                status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, None, stream),
                 "eags_forward_geom_bucketed")
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(device))
@@ -333,7 +365,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
             return color, depth, third, radii, n_touched, state
         if mode == "nosync":
             _check_pending(idx)
-            slot = torch.zeros(1, dtype=torch.int64).pin_memory()
+            slot = _nosync_slot()
         else:
             slot = _pinned_slot()
         _lib.check(lib.eags_forward_geom(C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(),
@@ -400,8 +432,8 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
             dL_dcolor = torch.zeros(3, H, W, **f32)
         if dL_ddepth is None:
             dL_ddepth = torch.zeros(1, H, W, **f32)
-        arena = _arena or {}
-        route = _peer_route if not pose_only else None
+        arena = _arena.get(device.index) or {}
+        route = _peer_route.get(device.index) if not pose_only else None
         route_final = True
         if route is not None:
             ex = route.ex
@@ -522,7 +554,8 @@ class _Rasterize(torch.autograd.Function):
         ctx.state = state
         ctx.has = [t is not None and t.numel() > 0 for t in
                    (shs, colors_precomp, scales, rotations, cov3D_precomp)]
-        ctx.want_tau = theta is not None or rho is not None
+        ctx.want_theta, ctx.want_rho = theta is not None, rho is not None
+        ctx.want_tau = ctx.want_theta or ctx.want_rho
         ctx.save_for_backward(*[t if t is not None else torch.empty(0) for t in
                                 (means3D, opacities, shs, colors_precomp, scales, rotations,
                                  cov3D_precomp)])
@@ -540,9 +573,9 @@ class _Rasterize(torch.autograd.Function):
         needs = ctx.needs_input_grad
         if st.P == 0:
             z = lambda t: None if t is None else torch.zeros_like(t)
-            tau = torch.zeros(3, device=st.radii.device) if ctx.want_tau else None
+            z3 = lambda want: torch.zeros(3, device=st.radii.device) if want else None
             return (z(means3D), None, z(shs), z(colors_precomp), z(opacities), z(scales), z(rotations),
-                    z(cov3D), tau, tau, None, None)
+                    z(cov3D), z3(ctx.want_theta), z3(ctx.want_rho), None, None)
         # variant B upstream drops the gradient of the opacity image; variant A carries dL/dalpha
         g_third = g_third if st.variant == _lib.VARIANT_A else None
         # registration (src/gsr/solver.py) optimises the pose only: no per-Gaussian gradient is written then
@@ -550,12 +583,12 @@ class _Rasterize(torch.autograd.Function):
         out = rasterize_backward(ctx.settings, st, means3D, opacities, shs, colors_precomp, scales,
                                  rotations, cov3D, g_color, g_depth, g_third,
                                  want_shs=bool(needs[2]), want_tau=ctx.want_tau, pose_only=pose_only)
-        if pose_only:
-            tau = out["tau"]
-            return (None, None, None, None, None, None, None, None, tau[3:], tau[:3], None, None)
+        # a gradient only for the pose slots that were given a tensor (theta alone or rho alone is legal)
         tau = out["tau"]
-        g_rho = tau[:3] if tau is not None else None
-        g_theta = tau[3:] if tau is not None else None
+        g_rho = tau[:3] if (tau is not None and ctx.want_rho) else None
+        g_theta = tau[3:] if (tau is not None and ctx.want_theta) else None
+        if pose_only:
+            return (None, None, None, None, None, None, None, None, g_theta, g_rho, None, None)
         return (out["means3D"], out["means2D"], out["shs"], out["colors_precomp"],
                 out["opacities"].view(opacities.shape) if out["opacities"] is not None else None,
                 out["scales"], out["rotations"], out["cov3D_precomp"], g_theta, g_rho, None, None)

@@ -141,7 +141,11 @@ int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int3
  * bytes and is needed BEFORE stage 1) and stage 2 launches no duplicate kernel.  The whole 64-byte
  * status block is copied to pinned memory.  If `bucket_overflow` comes back non-zero (or
  * num_rendered > capacity) nothing was rendered: re-issue stage 2 with eags_forward_render (exact
- * path; the tile scan of stage 1 is still valid).  tile_cap == 0 degenerates to the exact path. */
+ * path; the tile scan of stage 1 is still valid).  tile_cap == 0 degenerates to the exact path.
+ * `sticky_status_dev` (optional, device, 64 bytes, zeroed ONCE by the caller and never by the library): when
+ * given, num_rendered / max_tile are folded into it with atomicMax and bucket_overflow with atomicOr, and
+ * THAT block is what is copied to `status_pinned` -- for CUDA-graph replays, where the host looks at the
+ * status once per many replays and an overflow of any of them must still be seen. */
 typedef struct EagsForwardStatus {
     uint64_t num_rendered;    /* K = sum(tiles_touched)                                   */
     uint64_t num_scanned;
@@ -158,7 +162,7 @@ size_t eags_binning_state_bytes_bucketed(int64_t capacity, int32_t with_keys, in
 int eags_forward_geom_bucketed(const EagsView* view, const EagsGaussians* g, void* geom_state,
                                void* image_state, int32_t* radii, EagsForwardStatus* status_pinned,
                                void* binning_state, int64_t capacity, int32_t with_keys,
-                               int32_t tile_cap, void* stream);
+                               int32_t tile_cap, EagsForwardStatus* sticky_status_dev, void* stream);
 int eags_forward_render_bucketed(const EagsView* view, const EagsGaussians* g, const int32_t* radii,
                                  void* geom_state, void* image_state, void* binning_state,
                                  int64_t capacity, int32_t with_keys, int32_t tile_cap,
