@@ -121,15 +121,29 @@ class ShardedMapper:
     mapper.py:166) added once, on every rank identically, after the all-reduce division.
     """
 
-    def __init__(self, params: Sequence[torch.Tensor], optimizer: torch.optim.Optimizer,
-                 broadcast: bool = True, exchange=None, exchanged: Sequence[torch.Tensor] = ()):
+    def __init__(self, params: Sequence[torch.Tensor], optimizer: Optional[torch.optim.Optimizer],
+                 broadcast: bool = True, exchange=None, exchanged: Sequence[torch.Tensor] = (),
+                 fused_optimizer=None, check_every: int = 50):
         """``exchange`` (:class:`eags_raster.peer.PeerGradExchange`) moves the gradients of the
         rasterizer's xyz / scale / rotation / opacity inputs over NVLink peer memory inside the backward
         kernel; ``exchanged`` names the parameters that receive gradient ONLY through those four inputs
         (e.g. ``_xyz, _scaling, _rotation, _opacity``, gaussian_model.py:60-79) -- they are left out of the
-        NCCL bucket, which then carries just the rest (e.g. the SH features)."""
+        NCCL bucket, which then carries just the rest (e.g. the SH features).
+
+        ``fused_optimizer`` (:class:`eags_raster.peer.PeerAdam`) owns xyz / scaling / rotation / opacity
+        itself (raw parameters inside the exchange, Adam moments on the owner rank) and takes their step
+        inside the exchange kernel; ``params`` / ``optimizer`` then cover only the REST (e.g. SH features;
+        both may be empty / None).  ``loss_fn`` must render with ``fused_optimizer.activated()``.
+
+        Every ``check_every`` steps (a host sync) the exchange's error word is read and
+        :class:`eags_raster.peer.PeerExchangeError` raised if a peer ever failed to arrive: the failed step
+        delivered NaN (reduce) or skipped its update (fused step), never a partial sum."""
         self.optimizer = optimizer
         self.exchange = exchange
+        self.fused_optimizer = fused_optimizer
+        self.check_every, self._steps = int(check_every), 0
+        if fused_optimizer is not None and fused_optimizer.ex is not exchange:
+            raise ValueError("ShardedMapper: fused_optimizer must be built on the same exchange=")
         self._exchanged_ids = {id(p) for p in exchanged}
         if exchange is None and self._exchanged_ids:
             raise ValueError("ShardedMapper: exchanged= needs exchange=")
@@ -173,7 +187,8 @@ class ShardedMapper:
                                  "every rank must render at least one per step")
             for p in self._routed:
                 p.grad = None        # the routed pass returns the all-rank result; nothing to add it to
-            with self.exchange.route(scale=1.0 / len(views), local_views=len(mine)):
+            with self.exchange.route(scale=1.0 / len(views), local_views=len(mine),
+                                     optimizer=self.fused_optimizer):
                 render_all()
         else:
             render_all()
@@ -181,5 +196,9 @@ class ShardedMapper:
             self.bucket.all_reduce(divide_by=float(len(views)))
         if reg_fn is not None:
             reg_fn().backward()      # accumulates into the (already averaged) gradients, same on all ranks
-        self.optimizer.step()
+        if self.optimizer is not None:
+            self.optimizer.step()
+        self._steps += 1
+        if self.exchange is not None and self.check_every > 0 and self._steps % self.check_every == 0:
+            self.exchange.check()    # raises if any exchange since the last check lost a peer
         return {"local_loss_sum": local, "local_views": len(mine)}

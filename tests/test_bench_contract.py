@@ -34,6 +34,22 @@ def test_reference_arm_prints_one_json_line_with_the_contract_keys():
     assert d["gpu_launches"] == 0 and d["vs_baseline"] is None and d["dtype"] == "f32" and d["data"] == "synthetic"
 
 
+def test_reference_arm_honours_steps_and_mirrors_the_mapping_config():
+    """N > 1: the reference arm times the mapping workload (one view of the 8-view batch per step) with the
+    product arm's config / metric / unit, and runs exactly the steps it was asked for."""
+    r = _run(["--impl", "reference", "--gpus", "2", "--steps", "3", "--warmup", "1", "--mapping-workload", "tiny"],
+             env={"RANK": "0", "LOCAL_RANK": "0", "WORLD_SIZE": "2"})
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and d["steps"] == 3 and d["warmup"] == 1 and d["n_gpus"] == 2
+    assert d["unit"] == "views/s" and d["scaling"] == "strong" and d["metric"].startswith("mapping it/s")
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "eags-slam_b200")]
+    import bench
+    from eags_raster import scene
+    assert d["config"] == bench.mapping_config("tiny", scene.workload_camera("tiny"), 300)
+    assert "upstream_cuda_rasterizer" in d and d["e2e"]["value"] == d["value"]
+
+
 def test_reference_arm_other_ranks_exit_without_work():
     r = _run(["--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1"],
              env={"RANK": "1", "LOCAL_RANK": "1", "WORLD_SIZE": "2"}, timeout=120)

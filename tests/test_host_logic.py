@@ -96,7 +96,7 @@ def test_sharded_mapper_splits_parameters_between_exchange_and_bucket():
 
     out = m.step([1.0, 2.0, 3.0], loss_fn)
     assert seen == [1.0, 2.0, 3.0] and out["local_views"] == 3
-    assert ex.log[0] == ("enter", {"scale": 1.0 / 3, "local_views": 3}) and ex.log[-1][0] == "exit"
+    assert ex.log[0] == ("enter", {"scale": 1.0 / 3, "local_views": 3, "optimizer": None}) and ex.log[-1][0] == "exit"
     # the bucket parameter carries the mean over views (world 1): (1 + 2 + 3) / 3 = 2 -> 1 - 0.5 * 2 = 0
     assert torch.allclose(feat.detach(), torch.zeros(5, 3))
     with pytest.raises(ValueError, match="needs exchange"):
