@@ -194,6 +194,14 @@ def test_variant_b_pose_gradient_through_theta_rho():
     (((c2 * wc)[:, okt]).sum() + ((d2 * wd)[:, okt]).sum()).backward()
     assert rel_err(th2.grad.cpu().numpy(), theta.grad.cpu().numpy()) < 1e-5
     assert rel_err(rh2.grad.cpu().numpy(), rho.grad.cpu().numpy()) < 1e-5
+    # only ONE of the two pose slots given (backward must return None for the other, not a tensor)
+    th3 = torch.nn.Parameter(torch.zeros(3, device=DEV))
+    c3, _, d3, _, _ = GaussianRasterizer(raster_settings=s)(
+        means3D=frozen["means3D"], means2D=torch.zeros_like(frozen["means3D"]), shs=frozen["shs"], colors_precomp=None,
+        opacities=frozen["opacities"], scales=frozen["scales"], rotations=frozen["rotations"], cov3D_precomp=None,
+        theta=th3, rho=None)
+    (((c3 * wc)[:, okt]).sum() + ((d3 * wd)[:, okt]).sum()).backward()
+    assert rel_err(th3.grad.cpu().numpy(), theta.grad.cpu().numpy()) < 1e-5
 
 
 
