@@ -309,6 +309,16 @@ int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, con
     return 0;
 }
 
+int eags_pose_se3_update(float* theta, float* rho, float* viewmatrix, const float* projmatrix_raw,
+                         float* projmatrix_out, float* campos_out, float* tau_norm, void* stream) {
+    if (!theta || !rho || !viewmatrix || !projmatrix_raw || !projmatrix_out || !campos_out)
+        return fail(EAGS_ERR_INVALID, "eags_pose_se3_update: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_pose_se3_update(theta, rho, viewmatrix, projmatrix_raw, projmatrix_out, campos_out, tau_norm, s),
+                 "pose_se3_update");
+    return 0;
+}
+
 size_t eags_image_l1_scratch_bytes(int32_t W, int32_t H) { return image_l1_scratch_bytes(W, H); }
 
 int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,

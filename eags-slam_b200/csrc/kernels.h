@@ -102,6 +102,9 @@ int launch_pose_compose(const float* q, const float* t, const float* view, const
 int launch_pose_chain(const float* q, const float* t, const float* view, const float* dtau, float* dq,
                       float* dt, cudaStream_t s);
 
+int launch_pose_se3_update(float* theta, float* rho, float* view, const float* proj_raw, float* proj_out,
+                           float* campos_out, float* tau_norm, cudaStream_t s);
+
 // knn.cu
 size_t neighbors_workspace_bytes(long long n_ref);
 int launch_knn_mean_dist2(const float* pts, int n, float* out, void* ws, cudaStream_t s);

@@ -102,7 +102,75 @@ __global__ void pose_chain_kernel(const float* __restrict__ q, const float* __re
     for (int i = 0; i < 3; i++) dt[i] = grp[i];
 }
 
+// K13 pose_se3_update: the per-iteration camera update of loop-closure registration
+// (reference src/utils/pose_utils.py:76-93 update_pose + the properties of src/gsr/camera.py:97-111):
+//   w2c <- SE3_exp([rho, theta]) w2c  (pose_utils.py:40-74: Rodrigues rotation, V(theta) rho, the small-angle
+//   series below 1e-5), viewmatrix = w2c^T, projmatrix = viewmatrix projmatrix_raw, campos = -R^T t,
+//   theta, rho <- 0.  One thread; replaces ~25 tiny torch kernels and the host round trip per iteration.
+__global__ void pose_se3_update_kernel(float* __restrict__ theta, float* __restrict__ rho,
+                                       float* __restrict__ view, const float* __restrict__ proj_raw,
+                                       float* __restrict__ proj_out, float* __restrict__ campos_out,
+                                       float* __restrict__ tau_norm) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const float th[3] = {theta[0], theta[1], theta[2]}, rh[3] = {rho[0], rho[1], rho[2]};
+    const float W[3][3] = {{0.f, -th[2], th[1]}, {th[2], 0.f, -th[0]}, {-th[1], th[0], 0.f}};
+    float W2[3][3];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) W2[i][j] = W[i][0] * W[0][j] + W[i][1] * W[1][j] + W[i][2] * W[2][j];
+    const float angle = sqrtf(th[0] * th[0] + th[1] * th[1] + th[2] * th[2]);
+    float a1, a2, b1, b2;   // R = I + a1 W + a2 W2 ; V = I + b1 W + b2 W2
+    if (angle < 1e-5f) {
+        a1 = 1.f; a2 = 0.5f; b1 = 0.5f; b2 = 1.f / 6.f;
+    } else {
+        a1 = sinf(angle) / angle;
+        a2 = (1.f - cosf(angle)) / (angle * angle);
+        b1 = a2;
+        b2 = (angle - sinf(angle)) / (angle * angle * angle);
+    }
+    float E[3][3], Vm[3][3], te[3];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            const float I = i == j ? 1.f : 0.f;
+            E[i][j] = I + a1 * W[i][j] + a2 * W2[i][j];
+            Vm[i][j] = I + b1 * W[i][j] + b2 * W2[i][j];
+        }
+    for (int i = 0; i < 3; i++) te[i] = Vm[i][0] * rh[0] + Vm[i][1] * rh[1] + Vm[i][2] * rh[2];
+    // old w2c = [R | t] from viewmatrix = w2c^T
+    float R[3][3], t[3], Rn[3][3], tn[3];
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) R[i][j] = view[j * 4 + i];
+        t[i] = view[3 * 4 + i];
+    }
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) Rn[i][j] = E[i][0] * R[0][j] + E[i][1] * R[1][j] + E[i][2] * R[2][j];
+        tn[i] = E[i][0] * t[0] + E[i][1] * t[1] + E[i][2] * t[2] + te[i];
+    }
+    float Vn[16];
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) Vn[j * 4 + i] = Rn[i][j];
+        Vn[3 * 4 + i] = tn[i];
+        Vn[i * 4 + 3] = 0.f;
+    }
+    Vn[15] = 1.f;
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) {
+            float acc = 0.f;
+            for (int k = 0; k < 4; k++) acc += Vn[i * 4 + k] * proj_raw[k * 4 + j];
+            proj_out[i * 4 + j] = acc;
+        }
+    for (int k = 0; k < 16; k++) view[k] = Vn[k];
+    for (int i = 0; i < 3; i++) campos_out[i] = -(Rn[0][i] * tn[0] + Rn[1][i] * tn[1] + Rn[2][i] * tn[2]);
+    if (tau_norm) *tau_norm = sqrtf(angle * angle + rh[0] * rh[0] + rh[1] * rh[1] + rh[2] * rh[2]);
+    for (int i = 0; i < 3; i++) { theta[i] = 0.f; rho[i] = 0.f; }
+}
+
 }  // namespace
+
+int launch_pose_se3_update(float* theta, float* rho, float* view, const float* proj_raw, float* proj_out,
+                           float* campos_out, float* tau_norm, cudaStream_t s) {
+    pose_se3_update_kernel<<<1, 32, 0, s>>>(theta, rho, view, proj_raw, proj_out, campos_out, tau_norm);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
 
 int launch_pose_compose(const float* q, const float* t, const float* view, const float* proj,
                         const float* campos, float* view_out, float* proj_out, float* campos_out,

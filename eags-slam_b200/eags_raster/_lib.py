@@ -114,6 +114,7 @@ SIGNATURES = {
     "eags_isotropic_loss": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_pose_compose": (C.c_int, [C.c_void_p] * 9),
     "eags_pose_chain": (C.c_int, [C.c_void_p] * 7),
+    "eags_pose_se3_update": (C.c_int, [C.c_void_p] * 8),
     "eags_neighbors_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "eags_knn_mean_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "eags_radius_has_neighbor": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_float, C.c_void_p,

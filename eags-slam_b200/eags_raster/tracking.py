@@ -97,3 +97,26 @@ def render_relative(settings, means3D, opacities, shs, scales, rotations, cam_ro
     as ``opt_cam_rot`` in tracker.py:85; cam_trans) seen from ``settings``' camera.  Returns
     ``(color, depth, alpha, radii)``; gradients flow to ``cam_rot`` and ``cam_trans`` only."""
     return _RenderRelative.apply(cam_rot, cam_trans, means3D, opacities, shs, scales, rotations, settings)
+
+
+def update_pose_se3(theta: torch.Tensor, rho: torch.Tensor, viewmatrix: torch.Tensor, projmatrix_raw: torch.Tensor,
+                    projmatrix: torch.Tensor, campos: torch.Tensor, tau_norm: torch.Tensor = None) -> None:
+    """The per-iteration camera update of loop-closure registration, on the device and in place: the
+    reference's ``update_pose(viewpoint)`` (src/utils/pose_utils.py:76-93: ``w2c <- SE3_exp([rho, theta]) @ w2c``,
+    deltas zeroed) plus the recomputation of ``world_view_transform`` / ``full_proj_transform`` /
+    ``camera_center`` (src/gsr/camera.py:97-111).  ``viewmatrix`` (= w2c^T), ``projmatrix`` and ``campos`` are
+    the tensors the rasterizer settings hold: they are overwritten, so a CUDA-graph replay of the iteration sees
+    the new camera.  ``tau_norm`` (1-element device tensor) receives ``|tau|`` -- the reference's convergence
+    test reads it (``< 1e-4``) without forcing a sync per iteration."""
+    lib = _lib.load()
+    dev = theta.device
+    for name, x, n in (("theta", theta, 3), ("rho", rho, 3), ("viewmatrix", viewmatrix, 16),
+                       ("projmatrix_raw", projmatrix_raw, 16), ("projmatrix", projmatrix, 16), ("campos", campos, 3)):
+        if not (x.is_cuda and x.device == dev and x.dtype == torch.float32 and x.is_contiguous() and x.numel() == n):
+            raise ValueError(f"update_pose_se3: {name} must be a contiguous fp32 CUDA tensor of {n} elements on {dev}")
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(lib.eags_pose_se3_update(theta.data_ptr(), rho.data_ptr(), viewmatrix.data_ptr(),
+                                            projmatrix_raw.data_ptr(), projmatrix.data_ptr(), campos.data_ptr(),
+                                            None if tau_norm is None else tau_norm.data_ptr(), stream),
+                   "eags_pose_se3_update")

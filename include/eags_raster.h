@@ -305,6 +305,16 @@ int eags_pose_compose(const float* q, const float* t, const float* viewmatrix, c
 int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, const float* dL_dtau,
                     float* dL_dq, float* dL_dt, void* stream);
 
+/* Camera update of loop-closure registration (variant B call site): the reference's update_pose
+ * (src/utils/pose_utils.py:76-93) followed by the view / projection / centre properties of
+ * src/gsr/camera.py:97-111, on the device and in place:
+ *   w2c <- SE3_exp([rho, theta]) w2c  (pose_utils.py:40-74), viewmatrix = w2c^T (updated in place),
+ *   projmatrix_out = viewmatrix x projmatrix_raw, campos_out = camera centre, theta = rho = 0;
+ * tau_norm (nullable, device float) receives |[rho, theta]| -- the reference's convergence measure
+ * (`tau.norm() < 1e-4`), readable whenever the host chooses to look.  All pointers device fp32. */
+int eags_pose_se3_update(float* theta, float* rho, float* viewmatrix, const float* projmatrix_raw,
+                         float* projmatrix_out, float* campos_out, float* tau_norm, void* stream);
+
 /* ---- Neighbour queries around keyframe seeding -------------------------------
  * eags_knn_mean_dist2 replaces `simple_knn._C.distCUDA2(points)` (un-vendored pip dependency
  * `simple-knn`; reference call sites src/entities/gaussian_model.py:143,146,253,257,298,301,616):
