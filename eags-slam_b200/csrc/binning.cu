@@ -247,7 +247,7 @@ constexpr int RADIX_DIGITS = 1 << RADIX_BITS;
 constexpr int TIE_RUN_MAX = 32;   // longer runs of exactly equal depth go to the bitonic fallback
 
 template <int THREADS>
-struct RadixSmem {
+struct alignas(16) RadixSmem {
     unsigned cnt[(THREADS / 32) * RADIX_DIGITS];   // [warp][digit]
     unsigned base[RADIX_DIGITS];
     unsigned wmin[32], wmax[32], wtot[8];
@@ -382,10 +382,108 @@ __device__ __forceinline__ bool radix_sort_tile(unsigned* s_key, unsigned* s_val
     return !__syncthreads_or(too_long);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Per-tile bucket sort (the default): ONE counting pass + a thread-local finish.
+// ------------------------------------------------------------------------------------------------
+// The radix sort above is latency-bound (three dependent passes of shared-memory ranking per tile).  A
+// tile's keys are spread over its own depth range, so one pass that scatters them into NB = 8 x THREADS
+// equal sub-ranges of [min, max] (shared-memory atomics: the order inside a bucket does not matter) leaves
+// buckets of ~0.4 keys; thread t then finishes its 8 adjacent buckets -- a handful of keys -- with an
+// insertion sort on (depth bits, Gaussian index), which also settles exact depth ties in upstream's
+// emission order.  Depths that cluster (more than BUCKET_RUN_MAX keys in one thread's range) send the tile
+// to the radix sort instead.  The counters reuse the radix sort's [warp][digit] array.
+constexpr int BUCKET_RUN_MAX = 32;
+
+template <int THREADS, int ITEMS>
+__device__ __forceinline__ bool bucket_sort_tile(unsigned* s_key, unsigned* s_val, RadixSmem<THREADS>& sm,
+                                                 const u64* __restrict__ src, int n) {
+    constexpr int NW = THREADS / 32, PER = 8, NB = THREADS * PER;
+    static_assert(NB == NW * RADIX_DIGITS, "the bucket counters alias the radix counters");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned* cnt = sm.cnt;
+    unsigned key[ITEMS], val[ITEMS];
+    unsigned kmin = 0xffffffffu, kmax = 0u;
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++) {
+        key[r] = 0u; val[r] = 0u;
+        const int p = tid + r * THREADS;
+        if (p < n) {
+            const u64 k = src[p];
+            key[r] = (unsigned)(k >> 32);
+            val[r] = (unsigned)k;
+            kmin = min(kmin, key[r]);
+            kmax = max(kmax, key[r]);
+        }
+    }
+    {   // zero the counters while the loads are in flight
+        uint4* c4 = reinterpret_cast<uint4*>(cnt);
+        c4[2 * tid] = make_uint4(0u, 0u, 0u, 0u);
+        c4[2 * tid + 1] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if (lane == 0) { sm.wmin[warp] = kmin; sm.wmax[warp] = kmax; }
+    __syncthreads();
+    kmin = __reduce_min_sync(0xffffffffu, lane < NW ? sm.wmin[lane] : 0xffffffffu);
+    kmax = __reduce_max_sync(0xffffffffu, lane < NW ? sm.wmax[lane] : 0u);
+    const unsigned range = kmax - kmin;
+    const int nbits = range ? 32 - __clz(range) : 0;
+    constexpr int LOG_NB = 31 - __builtin_clz((unsigned)NB);
+    const int shift = nbits > LOG_NB ? nbits - LOG_NB : 0;
+    // ---- histogram
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++)
+        if (tid + r * THREADS < n) atomicAdd(&cnt[(key[r] - kmin) >> shift], 1u);
+    __syncthreads();
+    // ---- exclusive scan: thread t owns buckets [8 t, 8 t + 8)
+    uint4 ca = reinterpret_cast<uint4*>(cnt)[2 * tid], cb = reinterpret_cast<uint4*>(cnt)[2 * tid + 1];
+    const unsigned mine = ca.x + ca.y + ca.z + ca.w + cb.x + cb.y + cb.z + cb.w;
+    unsigned incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) sm.wmax[warp] = incl;                 // (wmin / wmax were consumed above)
+    const bool clustered = __syncthreads_or(mine > BUCKET_RUN_MAX);
+    if (clustered) return false;                          // nothing was written to s_key / s_val yet
+    unsigned base = incl - mine;
+    for (int w = 0; w < warp; w++) base += sm.wmax[w];
+    {
+        uint4 ea, eb;
+        ea.x = base; ea.y = ea.x + ca.x; ea.z = ea.y + ca.y; ea.w = ea.z + ca.z;
+        eb.x = ea.w + ca.w; eb.y = eb.x + cb.x; eb.z = eb.y + cb.y; eb.w = eb.z + cb.z;
+        reinterpret_cast<uint4*>(cnt)[2 * tid] = ea;      // the counters become the scatter cursors
+        reinterpret_cast<uint4*>(cnt)[2 * tid + 1] = eb;
+    }
+    __syncthreads();
+    // ---- scatter (arbitrary order inside a bucket)
+#pragma unroll
+    for (int r = 0; r < ITEMS; r++)
+        if (tid + r * THREADS < n) {
+            const unsigned pos = atomicAdd(&cnt[(key[r] - kmin) >> shift], 1u);
+            s_key[pos] = key[r];
+            s_val[pos] = val[r];
+        }
+    __syncthreads();
+    // ---- finish: insertion sort of this thread's run [base, base + mine) on (depth bits, index)
+    for (unsigned i = base + 1; i < base + mine; i++) {
+        const unsigned k = s_key[i], v = s_val[i];
+        unsigned j = i;
+        while (j > base) {
+            const unsigned pk = s_key[j - 1], pv = s_val[j - 1];
+            if (pk < k || (pk == k && pv < v)) break;
+            s_key[j] = pk; s_val[j] = pv;
+            j--;
+        }
+        s_key[j] = k; s_val[j] = v;
+    }
+    __syncthreads();
+    return true;
+}
+
 struct PackArgs {
-    const float2* xy;
-    const float4* conic_opacity;
-    const float4* rgbd;
+    const float4* splat_rec;   // [3P] per-Gaussian records written by preprocess_fwd
     uint32_t* point_list;
     float4* records;
     unsigned long long* keys;   // nullable
@@ -397,16 +495,13 @@ __device__ __forceinline__ void pack_sorted(Get get, int n, unsigned start, unsi
     for (int k = threadIdx.x; k < n; k += THREADS) {
         const uint2 e = get(k);
         const unsigned idx = e.y;
-        const float2 xy = a.xy[idx];
-        const float4 co = a.conic_opacity[idx];
-        const float4 cd = a.rgbd[idx];
+        const float4* __restrict__ g = a.splat_rec + (size_t)3 * idx;   // 48 contiguous bytes
+        const float4 g0 = g[0], g1 = g[1], g2 = g[2];
         const size_t o = (size_t)start + k;
         a.point_list[o] = idx;
-        // log2-scaled conic and the alpha >= 1/255 reach (blend.cu: record format)
-        const float L = 1.4426950408889634f;
-        a.records[3 * o + 0] = make_float4(xy.x, xy.y, __uint_as_float(idx), cd.w);
-        a.records[3 * o + 1] = make_float4(-0.5f * L * co.x, -L * co.y, -0.5f * L * co.z, co.w);
-        a.records[3 * o + 2] = make_float4(cd.x, cd.y, cd.z, __log2f(255.f * co.w));
+        a.records[3 * o + 0] = g0;
+        a.records[3 * o + 1] = g1;
+        a.records[3 * o + 2] = g2;
         if (a.keys) a.keys[o] = ((unsigned long long)tile << 32) | e.x;
     }
 }
@@ -418,7 +513,15 @@ __device__ __forceinline__ void sort_pack_tile(u64* s_keys, RadixSmem<THREADS>& 
                                                const PackArgs& a) {
     unsigned* s_key = reinterpret_cast<unsigned*>(s_keys);
     unsigned* s_val = s_key + THREADS * ITEMS;
-    if (use_radix && radix_sort_tile<THREADS, ITEMS>(s_key, s_val, sm, src, n)) {
+    // sort mode ("radix_sort" option): 0 bitonic on the 64-bit composite, 1 LSD radix, 2 (default) bucket
+    // sort with the radix sort behind it for clustered depths; each falls back to the next one down
+    bool done = false;
+    if (use_radix >= 2) done = bucket_sort_tile<THREADS, ITEMS>(s_key, s_val, sm, src, n);
+    if (!done && use_radix >= 1) {
+        __syncthreads();
+        done = radix_sort_tile<THREADS, ITEMS>(s_key, s_val, sm, src, n);
+    }
+    if (done) {
         pack_sorted<THREADS>([=](int k) { return make_uint2(s_key[k], s_val[k]); }, n, start, tile, a);
     } else {
         __syncthreads();
@@ -488,7 +591,7 @@ int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s) {
 int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
                      cudaStream_t s) {
     PackArgs a;
-    a.xy = geom.xy; a.conic_opacity = geom.conic_opacity; a.rgbd = geom.rgbd;
+    a.splat_rec = geom.splat_rec;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
     sort_pack_small_kernel<<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;

@@ -13,7 +13,7 @@ namespace {
 thread_local char g_err[512] = "";
 std::atomic<int> g_opt_tma{1};
 std::atomic<int> g_opt_agg{1};
-std::atomic<int> g_opt_radix{1};
+std::atomic<int> g_opt_radix{2};
 std::atomic<int> g_opt_stats{0};
 std::atomic<unsigned long long> g_launches{0};
 
@@ -96,7 +96,7 @@ int eags_set_option(const char* name, int32_t value) {
     if (name && !strcmp(name, "tma")) { g_opt_tma.store(value ? 1 : 0); return 0; }
     if (name && !strcmp(name, "kernel_timing")) { g_opt_timing.store(value ? 1 : 0); return 0; }
     if (name && !strcmp(name, "preprocess_agg")) { g_opt_agg.store(value ? 1 : 0); return 0; }
-    if (name && !strcmp(name, "radix_sort")) { g_opt_radix.store(value ? 1 : 0); return 0; }
+    if (name && !strcmp(name, "radix_sort")) { g_opt_radix.store(value < 0 ? 0 : (value > 2 ? 2 : value)); return 0; }
     if (name && !strcmp(name, "kernel_stats")) { g_opt_stats.store(value ? 1 : 0); return 0; }
     return fail(EAGS_ERR_INVALID, "eags_set_option: unknown option");
 }
@@ -416,9 +416,7 @@ int eags_state_view(const char* what, int32_t P, int32_t W, int32_t H, int64_t c
     const char* bb = (const char*)binning_state;
     struct Row { const char* name; const char* base; size_t off; int64_t n; int32_t eb; };
     const Row rows[] = {
-        {"xy", gb, GL.xy, P, 8},
-        {"conic_opacity", gb, GL.conic_opacity, P, 16},
-        {"rgbd", gb, GL.rgbd, P, 16},
+        {"splat_rec", gb, GL.splat_rec, (int64_t)P * 3, 16},
         {"tiles_touched", gb, GL.tiles_touched, P, 4},
         {"clamped", gb, GL.clamped, P, 1},
         {"ctrl", ib, IL.ctrl, 1, 64},

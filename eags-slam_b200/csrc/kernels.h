@@ -7,9 +7,7 @@
 #include "layout.h"
 
 struct GeomPtrs {
-    float2* xy;
-    float4* conic_opacity;
-    float4* rgbd;
+    float4* splat_rec;   // [3P], see layout.h
     uint32_t* tiles_touched;
     uint8_t* clamped;
 };
@@ -35,9 +33,7 @@ static inline GeomPtrs geom_ptrs(void* base, int64_t P) {
     GeomLayout L = geom_layout(P);
     char* b = (char*)base;
     GeomPtrs g;
-    g.xy = (float2*)(b + L.xy);
-    g.conic_opacity = (float4*)(b + L.conic_opacity);
-    g.rgbd = (float4*)(b + L.rgbd);
+    g.splat_rec = (float4*)(b + L.splat_rec);
     g.tiles_touched = (uint32_t*)(b + L.tiles_touched);
     g.clamped = (uint8_t*)(b + L.clamped);
     return g;

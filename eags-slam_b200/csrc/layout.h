@@ -4,9 +4,12 @@
 // stream with unit stride and 16-byte vectors):
 //
 //   geom state   (per Gaussian, written by preprocess_fwd)
-//     xy            float2[P]   pixel-space mean
-//     conic_opacity float4[P]   inverse 2-D covariance (xx, xy, yy) + opacity
-//     rgbd          float4[P]   SH->RGB colour and view-space depth
+//     splat_rec     float4[3P]  the splat record of every visible Gaussian, ALREADY in the form the blend
+//                               kernels stream (blend.cu): {x, y, bits(index), depth} {A, B, C, opacity}
+//                               {r, g, b, log2(255 opacity)} with (A, B, C) the conic pre-scaled by -log2(e)/2,
+//                               -log2(e), -log2(e)/2 -- written once per Gaussian by preprocess_fwd, so that
+//                               sort_pack copies 48 contiguous bytes per key instead of gathering from three
+//                               arrays and redoing the scaling K / P times
 //     tiles_touched u32[P]
 //     clamped       u8[P]       bit c: colour channel c was clamped at 0 (gates dL/dsh)
 //
@@ -57,14 +60,12 @@ static_assert(sizeof(EagsCtrl) == 64, "ctrl block is 64 bytes");
 static inline size_t eags_align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct GeomLayout {
-    size_t xy, conic_opacity, rgbd, tiles_touched, clamped, total;
+    size_t splat_rec, tiles_touched, clamped, total;
 };
 static inline GeomLayout geom_layout(int64_t P) {
     GeomLayout L;
     size_t o = 0;
-    L.xy = o;            o += eags_align256((size_t)P * 8);
-    L.conic_opacity = o; o += eags_align256((size_t)P * 16);
-    L.rgbd = o;          o += eags_align256((size_t)P * 16);
+    L.splat_rec = o;     o += eags_align256((size_t)P * 48);
     L.tiles_touched = o; o += eags_align256((size_t)P * 4);
     L.clamped = o;       o += eags_align256((size_t)P);
     L.total = o + 256;

@@ -80,10 +80,13 @@ __device__ __forceinline__ void emit_one(const PreArgs& a, const GeomPtrs& geom,
         float cp[3] = {__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)};
         sh_to_rgb(a.degree, s.p, cp, sh_row, rgb, clamped);
     }
-    geom.xy[i] = make_float2(s.px, s.py);
-    s.con.w = a.opacities[i];
-    geom.conic_opacity[i] = s.con;
-    geom.rgbd[i] = make_float4(rgb[0], rgb[1], rgb[2], s.depth);
+    // the record in the form the blend kernels read (blend.cu): log2-scaled conic, alpha >= 1/255 reach
+    const float opacity = a.opacities[i];
+    const float L = 1.4426950408889634f;
+    float4* rec = geom.splat_rec + (size_t)3 * i;
+    rec[0] = make_float4(s.px, s.py, __uint_as_float((unsigned)i), s.depth);
+    rec[1] = make_float4(-0.5f * L * s.con.x, -L * s.con.y, -0.5f * L * s.con.z, opacity);
+    rec[2] = make_float4(rgb[0], rgb[1], rgb[2], __log2f(255.f * opacity));
     geom.clamped[i] = (uint8_t)clamped;
 }
 
@@ -234,10 +237,10 @@ preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
         for (int i = begin + tid; i < end; i += AGG_THREADS) {
             const int r = radii[i];
             if (r <= 0) continue;
-            const float2 xy = geom.xy[i];
-            const float depth = geom.rgbd[i].w;
+            const float4 r0 = geom.splat_rec[(size_t)3 * i];
+            const float depth = r0.w;
             int x0, y0, x1, y1;
-            tile_rect(xy.x, xy.y, r, a.gx, a.gy, x0, y0, x1, y1);
+            tile_rect(r0.x, r0.y, r, a.gx, a.gy, x0, y0, x1, y1);
             const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
             for (int y = y0; y < y1; y++)
                 for (int x = x0; x < x1; x++) {
@@ -274,10 +277,10 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, GeomP
     if (i >= P) return;
     const int r = radii[i];
     if (r <= 0) return;
-    const float2 xy = geom.xy[i];
-    const float depth = geom.rgbd[i].w;
+    const float4 r0 = geom.splat_rec[(size_t)3 * i];
+    const float depth = r0.w;
     int x0, y0, x1, y1;
-    tile_rect(xy.x, xy.y, r, gx, gy, x0, y0, x1, y1);
+    tile_rect(r0.x, r0.y, r, gx, gy, x0, y0, x1, y1);
     // depth > 0.2 is a positive float: its bit pattern orders like the value;
     // ties are broken by the Gaussian index == upstream's emission order inside one tile.
     const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;

@@ -334,7 +334,8 @@ int eags_radius_has_neighbor(const float* ref_points, int32_t n_ref, const float
 
 /* Introspection of the state buffers (parity tests, debugging).  `what` selects the array; the
  * function returns its device address, element count and element size.  Names:
- *   "xy" float2[P], "conic_opacity" float4[P], "rgbd" float4[P] (r,g,b,depth),
+ *   "splat_rec" float4[3P] ({x, y, bits(index), depth} {A, B, C, opacity} {r, g, b, log2(255 opacity)} per
+ *   Gaussian, the conic pre-scaled by -log2(e)/2, -log2(e), -log2(e)/2; valid where radii > 0),
  *   "tiles_touched" u32[P], "clamped" u8[P] (bit c = channel c clamped),
  *   "ranges" uint2[G], "tile_count" u32[G], "final_T" f32[N], "n_contrib" u32[N],
  *   "tile_max_contrib" u32[G], "point_list" u32[cap], "point_list_keys" u64[cap] (with_keys),
@@ -349,8 +350,9 @@ int eags_state_view(const char* what, int32_t P, int32_t width, int32_t height, 
  *              0: plain cooperative loads.                                                     */
 /*   "preprocess_agg" 1 (default): CTA-aggregated preprocess_fwd (shared-memory tile histogram, one global
  *              atomic per (CTA, touched tile)); 0: one global atomic per (Gaussian, tile) key.
- *   "radix_sort" 1 (default): per-tile LSD radix sort on the varying depth bits; 0: bitonic network on the
- *              64-bit (depth | index) composite.  Both settings give bit-identical results.
+ *   "radix_sort" per-tile sort: 2 (default) one-pass bucket sort over the tile's depth range + thread-local
+ *              insertion finish (clustered depths fall back to 1); 1: LSD radix sort on the varying depth
+ *              bits; 0: bitonic network on the 64-bit (depth | index) composite.  Bit-identical results.
  *   "kernel_stats" 1: the blend kernels count the work they really executed (post-cull) into
  *              EagsForwardStatus.stat_* / the backward scratch (bench.py's executed-work roofline);
  *              default 0 (the counting instantiations are never launched).                       */

@@ -2,7 +2,8 @@
 
 * ``preprocess_agg`` (CTA-aggregated preprocess_fwd: shared-memory tile histogram, one global atomic per
   (CTA, touched tile)) vs the one-atomic-per-key kernel;
-* ``radix_sort`` (per-tile LSD radix sort on the varying depth bits + tie fix-up by Gaussian index) vs the
+* ``radix_sort`` = 2 (one-pass bucket sort over the tile's depth range + thread-local insertion finish, the
+  default), 1 (per-tile LSD radix sort on the varying depth bits + tie fix-up by Gaussian index) vs 0, the
   bitonic network on the 64-bit (depth | index) composite;
 
 on the exact path (count -> scan -> duplicate -> sort) and on the bucketed path, for ordinary scenes and
@@ -40,7 +41,7 @@ def _all_variants(cam, sc, o):
     K, G = o["num_rendered"], o["grid"][0] * o["grid"][1]
     ref_imgs = None
     try:
-        for agg, radix, bucketed in itertools.product((0, 1), (0, 1), (False, True)):
+        for agg, radix, bucketed in itertools.product((0, 1), (0, 1, 2), (False, True)):
             _lib.set_option("preprocess_agg", agg)
             _lib.set_option("radix_sort", radix)
             rz.set_bucketed(bucketed)
@@ -65,7 +66,7 @@ def _all_variants(cam, sc, o):
                     assert torch.equal(a, b), tag
     finally:
         _lib.set_option("preprocess_agg", 1)
-        _lib.set_option("radix_sort", 1)
+        _lib.set_option("radix_sort", 2)
         rz.set_bucketed(True)
 
 
@@ -91,6 +92,19 @@ def test_agg_spans_more_than_one_cta_and_image_order():
         assert out[5].num_rendered == K
         np.testing.assert_array_equal(got["point_list"].cpu().numpy().view(np.uint32), o["point_list"], err_msg=order)
         np.testing.assert_array_equal(got["point_list_keys"].cpu().numpy().view(np.uint64), o["keys"], err_msg=order)
+
+
+def test_clustered_depths_fall_back_to_the_radix_sort():
+    """Two thin surfaces (depth spread 1e-3 of the tile's range each): most keys of a tile land in a few of the
+    bucket sort's sub-ranges, so the tile is handed to the radix sort -- same result."""
+    g = torch.Generator().manual_seed(9)
+    sc = scene.make_scene("c1", P=60_000, seed=9)
+    z_new = torch.where(torch.rand(60_000, generator=g) < 0.5, 1.5, 3.5) + 1e-3 * torch.rand(60_000, generator=g)
+    ratio = (z_new / sc["means3D"][:, 2].abs().clamp_min(1e-6))
+    front = sc["means3D"][:, 2] > 0
+    sc["means3D"] = torch.where(front[:, None], sc["means3D"] * ratio[:, None], sc["means3D"]).contiguous()
+    cam = scene.workload_camera("c1")
+    _all_variants(cam, sc, oracle_forward(cam, sc, skip_blend=True))
 
 
 def _tie_scene(P, run, seed=0):
