@@ -30,9 +30,19 @@ struct Splat {
     int r, x0, y0, x1, y1;
 };
 
+// Inputs of one Gaussian requested up front (the aggregating kernel): the scale / rotation / opacity / SH-DC
+// loads do not depend on the culls, so issuing them together with the mean costs one DRAM latency per
+// Gaussian instead of three.
+struct RawIn {
+    float sc[3];
+    float4 q;
+    float opacity;
+    float sh[3];
+};
+
 template <typename CamPtr>
-__device__ __forceinline__ bool project_one(const PreArgs& a, CamPtr V, CamPtr F, int i, Splat& s) {
-    s.p[0] = a.means3D[(size_t)3 * i]; s.p[1] = a.means3D[(size_t)3 * i + 1]; s.p[2] = a.means3D[(size_t)3 * i + 2];
+__device__ __forceinline__ bool project_one(const PreArgs& a, CamPtr V, CamPtr F, int i, Splat& s,
+                                            bool pre = false, const RawIn& in = RawIn()) {
     float pv[3];
     pv[0] = V[0] * s.p[0] + V[4] * s.p[1] + V[8] * s.p[2] + V[12];
     pv[1] = V[1] * s.p[0] + V[5] * s.p[1] + V[9] * s.p[2] + V[13];
@@ -44,7 +54,8 @@ __device__ __forceinline__ bool project_one(const PreArgs& a, CamPtr V, CamPtr F
     float pw = 1.0f / (hw + 0.0000001f);
     float ppx = hx * pw, ppy = hy * pw;
     float c6[6];
-    load_cov6(a, i, c6);
+    if (pre) cov3d_from_scale_rot(in.sc, a.scale_modifier, in.q, c6);
+    else load_cov6(a, i, c6);
     float fx = (float)a.W / (2.f * a.tanfovx);
     float fy = (float)a.H / (2.f * a.tanfovy);
     Ewa e;
@@ -69,10 +80,13 @@ __device__ __forceinline__ bool project_one(const PreArgs& a, CamPtr V, CamPtr F
 
 // colour + the per-Gaussian geom records of a surviving Gaussian
 __device__ __forceinline__ void emit_one(const PreArgs& a, const GeomPtrs& geom, int i, Splat& s,
-                                         const float* sh_row) {
+                                         const float* sh_row, bool pre = false, const RawIn& in = RawIn()) {
     float rgb[3];
     unsigned clamped = 0;
-    if (a.colors_precomp) {
+    if (pre) {
+        float cp[3] = {0.f, 0.f, 0.f};                 // degree 0: the view direction is not used
+        sh_to_rgb(0, s.p, cp, in.sh, rgb, clamped);
+    } else if (a.colors_precomp) {
         rgb[0] = a.colors_precomp[(size_t)3 * i];
         rgb[1] = a.colors_precomp[(size_t)3 * i + 1];
         rgb[2] = a.colors_precomp[(size_t)3 * i + 2];
@@ -81,7 +95,7 @@ __device__ __forceinline__ void emit_one(const PreArgs& a, const GeomPtrs& geom,
         sh_to_rgb(a.degree, s.p, cp, sh_row, rgb, clamped);
     }
     // the record in the form the blend kernels read (blend.cu): log2-scaled conic, alpha >= 1/255 reach
-    const float opacity = a.opacities[i];
+    const float opacity = pre ? in.opacity : a.opacities[i];
     const float L = 1.4426950408889634f;
     float4* rec = geom.splat_rec + (size_t)3 * i;
     rec[0] = make_float4(s.px, s.py, __uint_as_float((unsigned)i), s.depth);
@@ -107,6 +121,7 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     if (i < a.P) {
         float V[16], F[16];
         load_cam(a, V, F);
+        sp.p[0] = a.means3D[(size_t)3 * i]; sp.p[1] = a.means3D[(size_t)3 * i + 1]; sp.p[2] = a.means3D[(size_t)3 * i + 2];
         alive = project_one(a, (const float*)V, (const float*)F, i, sp);
     }
     // phase B (wide SH rows): the warp fetches the rows of its surviving Gaussians, coalesced
@@ -187,10 +202,14 @@ preprocess_fwd_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
 // random order, ~#tiles-per-span fewer when the submap is stored in image order (SLAM seeds Gaussians
 // from keyframe pixels, so neighbours in memory share tiles).  The order inside a bucket is arbitrary
 // either way: sort_pack orders by (depth, index).
-constexpr int AGG_THREADS = 1024;
-constexpr int AGG_MAX_TILES = 24 * 1024;   // 96 KB histogram
+#ifndef EAGS_AGG_THREADS
+#define EAGS_AGG_THREADS 1024
+#endif
+constexpr int AGG_THREADS = EAGS_AGG_THREADS;
+constexpr int AGG_CTAS_PER_SM = 1024 / AGG_THREADS;
+constexpr int AGG_MAX_TILES = 24 * 1024 / AGG_CTAS_PER_SM;   // <= 96 KB of histogram per SM
 
-__global__ void __launch_bounds__(AGG_THREADS, 1)
+__global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS_PER_SM)
 preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
                           uint32_t* __restrict__ tile_count, EagsCtrl* __restrict__ ctrl,
                           unsigned long long* __restrict__ bucket, unsigned tile_cap, int span) {
@@ -206,12 +225,23 @@ preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
     const int begin = blockIdx.x * span, end = min(a.P, begin + span);
     unsigned my_total = 0;
     // ---- phase 1
+    // the call shape of every reference call site (scale + rotation, SH degree 0): all inputs up front
+    const bool fast = !a.cov3D_precomp && !a.colors_precomp && a.degree == 0;   // kernel-uniform
     for (int i = begin + tid; i < end; i += AGG_THREADS) {
         Splat sp;
+        RawIn in;
         unsigned my_tiles = 0;
         int r_out = 0;
-        if (project_one(a, V, F, i, sp)) {
-            emit_one(a, geom, i, sp, a.colors_precomp ? nullptr : a.shs + (size_t)i * a.M * 3);
+        sp.p[0] = a.means3D[(size_t)3 * i]; sp.p[1] = a.means3D[(size_t)3 * i + 1]; sp.p[2] = a.means3D[(size_t)3 * i + 2];
+        if (fast) {
+            in.sc[0] = a.scales[(size_t)3 * i]; in.sc[1] = a.scales[(size_t)3 * i + 1]; in.sc[2] = a.scales[(size_t)3 * i + 2];
+            in.q = *reinterpret_cast<const float4*>(a.rotations + (size_t)4 * i);
+            in.opacity = a.opacities[i];
+            const float* shr = a.shs + (size_t)i * a.M * 3;
+            in.sh[0] = shr[0]; in.sh[1] = shr[1]; in.sh[2] = shr[2];
+        }
+        if (project_one(a, V, F, i, sp, fast, in)) {
+            emit_one(a, geom, i, sp, a.colors_precomp ? nullptr : a.shs + (size_t)i * a.M * 3, fast, in);
             r_out = sp.r;
             my_tiles = (unsigned)((sp.x1 - sp.x0) * (sp.y1 - sp.y0));
             for (int y = sp.y0; y < sp.y1; y++)
@@ -310,7 +340,8 @@ int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs ge
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         // one CTA per SM; spans are multiples of the CTA width so every pass of a CTA is fully coalesced
-        int span = (g.P + sms - 1) / sms;
+        const int ctas = sms * AGG_CTAS_PER_SM;
+        int span = (g.P + ctas - 1) / ctas;
         span = ((span + AGG_THREADS - 1) / AGG_THREADS) * AGG_THREADS;
         const int grid = (g.P + span - 1) / span;
         const size_t smem = ((size_t)img.G + 32) * sizeof(unsigned);
