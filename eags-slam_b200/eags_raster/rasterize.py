@@ -168,6 +168,20 @@ def _f32c(t: torch.Tensor, device) -> torch.Tensor:
     return out
 
 
+_size_cache = {}
+
+
+def _sizes(lib, name: str, *args) -> int:
+    """Memoised eags_*_bytes queries (pure functions of their arguments)."""
+    key = (name,) + args
+    v = _size_cache.get(key)
+    if v is None:
+        if len(_size_cache) > 4096:
+            _size_cache.clear()
+        v = _size_cache[key] = int(getattr(lib, name)(*args))
+    return v
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -208,7 +222,26 @@ def _round_capacity(k: int) -> int:
     return (k + 0xFFFF) & ~0xFFFF
 
 
+_view_cache = {}   # (id(settings), variant, device index) -> (settings, EagsView, keep)
+
+
 def _make_view(s, variant: int, device) -> tuple:
+    """EagsView of a settings tuple.  The struct holds POINTERS, so when every camera tensor is already a
+    contiguous fp32 tensor on the device (values may change in place, addresses do not) it is built once per
+    settings object and reused -- the tracking / mapping loops call with the same settings 100+ times."""
+    key = (id(s), variant, device.index)
+    hit = _view_cache.get(key)
+    if hit is not None and hit[0] is s:
+        return hit[1], hit[2]
+    v, keep, direct = _build_view(s, variant, device)
+    if direct and isinstance(s, tuple):      # NamedTuple settings are immutable; duck-typed objects are not cached
+        if len(_view_cache) > 256:
+            _view_cache.clear()          # plain host structs: nothing on the device refers to them
+        _view_cache[key] = (s, v, keep)
+    return v, keep
+
+
+def _build_view(s, variant: int, device) -> tuple:
     bg = _f32c(s.bg, device)
     vm = _f32c(s.viewmatrix, device)
     pm = _f32c(s.projmatrix, device)
@@ -219,7 +252,9 @@ def _make_view(s, variant: int, device) -> tuple:
                  float(s.scale_modifier), int(s.sh_degree), int(variant), int(bool(s.prefiltered)),
                  int(bool(s.debug)), bg.data_ptr(), vm.data_ptr(), pm.data_ptr(), _ptr(raw),
                  cp.data_ptr())
-    return v, (bg, vm, pm, cp, raw)   # keep the tensors alive while the struct is in use
+    srcs = (s.bg, s.viewmatrix, s.projmatrix, s.campos, getattr(s, "projmatrix_raw", None))
+    direct = all(a is b for a, b in zip(srcs, (bg, vm, pm, cp, raw)))
+    return v, (bg, vm, pm, cp, raw), direct   # keep the tensors alive while the struct is in use
 
 
 def _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D):
@@ -286,8 +321,8 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
         g = _make_gaussians(P, M, means3D, opacities, shs, colors_precomp, scales, rotations,
                             cov3D_precomp)
         u8 = dict(dtype=torch.uint8, device=device)
-        geom = torch.empty(lib.eags_geom_state_bytes(P), **u8)
-        image = torch.empty(lib.eags_image_state_bytes(W, H), **u8)
+        geom = torch.empty(_sizes(lib, "eags_geom_state_bytes", P), **u8)
+        image = torch.empty(_sizes(lib, "eags_image_state_bytes", W, H), **u8)
         radii = torch.empty(P, dtype=torch.int32, device=device)
         color = torch.empty(3, H, W, dtype=torch.float32, device=device)
         depth = torch.empty(1, H, W, dtype=torch.float32, device=device)
@@ -314,7 +349,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
             if tile_cap * G > _MAX_BUCKET_SLOTS:
                 tile_cap = 0
             status, sticky = cap_ctx.take_status(cap, device)
-            binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
+            binning = torch.empty(_sizes(lib, "eags_binning_state_bytes_bucketed", cap, int(with_keys), W, H, tile_cap), **u8)
             _lib.check(lib.eags_forward_geom_bucketed(
                 C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
                 status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, sticky.data_ptr(), stream),
@@ -336,7 +371,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
                 tile_cap = 0
             cap = _capacity.get(idx, 0) or _round_capacity(max(4 * P, _MIN_CAPACITY))
             status = _pinned_status()
-            binning = torch.empty(lib.eags_binning_state_bytes_bucketed(cap, int(with_keys), W, H, tile_cap), **u8)
+            binning = torch.empty(_sizes(lib, "eags_binning_state_bytes_bucketed", cap, int(with_keys), W, H, tile_cap), **u8)
             _lib.check(lib.eags_forward_geom_bucketed(
                 C.byref(view), C.byref(g), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
                 status.data_ptr(), binning.data_ptr(), cap, int(with_keys), tile_cap, None, stream),
@@ -354,7 +389,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
             if K > cap or overflow:
                 # nothing was rendered (every stage-2 kernel exited): re-issue stage 2 on the exact path
                 cap = max(cap, _round_capacity(int(K * 1.25)))
-                binning = torch.empty(lib.eags_binning_state_bytes(cap, int(with_keys)), **u8)
+                binning = torch.empty(_sizes(lib, "eags_binning_state_bytes", cap, int(with_keys)), **u8)
                 _lib.check(lib.eags_forward_render(C.byref(view), C.byref(g), radii.data_ptr(),
                                                    geom.data_ptr(), image.data_ptr(), binning.data_ptr(), cap,
                                                    int(with_keys), C.byref(imgs), stream), "eags_forward_render")
@@ -374,7 +409,7 @@ def rasterize_forward(settings, variant, means3D, opacities, shs=None, colors_pr
         ev.record(torch.cuda.current_stream(device))
 
         def render(cap):
-            b = torch.empty(lib.eags_binning_state_bytes(cap, int(with_keys)), **u8)
+            b = torch.empty(_sizes(lib, "eags_binning_state_bytes", cap, int(with_keys)), **u8)
             _lib.check(lib.eags_forward_render(C.byref(view), C.byref(g), radii.data_ptr(),
                                                geom.data_ptr(), image.data_ptr(), b.data_ptr(), cap,
                                                int(with_keys), C.byref(imgs), stream),
@@ -476,7 +511,7 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
         gout = EagsInputGrads(_ptr(out["means3D"]), _ptr(out["means2D"]), _ptr(out["opacities"]),
                               _ptr(out["shs"]), _ptr(out["colors_precomp"]), _ptr(out["scales"]),
                               _ptr(out["rotations"]), _ptr(out["cov3D_precomp"]), _ptr(out["tau"]))
-        scratch = torch.empty(lib.eags_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
+        scratch = torch.empty(_sizes(lib, "eags_backward_scratch_bytes", P), dtype=torch.uint8, device=device)
         if route is not None and route_final:
             # sharded mapping: xyz / scale / rotation / opacity gradients (plus the local sums of the
             # rank's earlier views of this step) are scattered to their owner ranks by preprocess_bwd
