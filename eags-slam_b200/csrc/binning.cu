@@ -28,7 +28,11 @@ namespace {
 // K2: single-CTA scan over G tile counts (G = 1 200 .. 8 030 for the benchmark shapes).
 // ------------------------------------------------------------------------------------------------
 constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_PER = 8;   // counters per thread and round: all eight loads are in flight together
 
+// One CTA; thread t of a round owns the SCAN_PER consecutive tiles [base + 8 t, base + 8 t + 8): the counters
+// sit one per 128-byte line, so a round costs ONE memory latency for 8 192 tiles (c2 - c4 need one round)
+// instead of one per 1 024.
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
     __shared__ unsigned s_warp[SCAN_THREADS / 32];
@@ -36,10 +40,16 @@ tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) { s_carry = 0; s_max = 0; }
     __syncthreads();
-    for (int base = 0; base < img.G; base += SCAN_THREADS) {
-        const int t = base + tid;
-        const unsigned c = (t < img.G) ? img.tile_count[(size_t)t * EAGS_CTR_STRIDE] : 0u;
-        unsigned incl = c;
+    for (int base = 0; base < img.G; base += SCAN_THREADS * SCAN_PER) {
+        const int t0 = base + tid * SCAN_PER;
+        unsigned c[SCAN_PER];
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; k++)
+            c[k] = (t0 + k < img.G) ? img.tile_count[(size_t)(t0 + k) * EAGS_CTR_STRIDE] : 0u;
+        unsigned mine = 0, mx = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; k++) { mine += c[k]; mx = max(mx, c[k]); }
+        unsigned incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             unsigned n = __shfl_up_sync(0xffffffffu, incl, o);
@@ -47,7 +57,7 @@ tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
         }
         if (lane == 31) s_warp[warp] = incl;
         {
-            const unsigned m = __reduce_max_sync(0xffffffffu, c);
+            const unsigned m = __reduce_max_sync(0xffffffffu, mx);
             if (lane == 0 && m) atomicMax(&s_max, m);
         }
         __syncthreads();
@@ -62,19 +72,23 @@ tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
             s_warp[lane] = wi - w;   // exclusive prefix of the warp totals
         }
         __syncthreads();
-        const unsigned carry = s_carry;
-        const unsigned start = carry + s_warp[warp] + incl - c;
-        if (t < img.G) {
-            img.ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
-            img.tile_count[(size_t)t * EAGS_CTR_STRIDE] = start;   // the counter becomes the scatter cursor
-            img.tile_max[t] = 0u;
-            if (c > EAGS_SORT_SMALL_CAP) {
-                unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
-                img.big_list[pos] = (unsigned)t;
+        unsigned start = s_carry + s_warp[warp] + incl - mine;
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; k++) {
+            const int t = t0 + k;
+            if (t < img.G) {
+                img.ranges[t] = c[k] ? make_uint2(start, start + c[k]) : make_uint2(0u, 0u);
+                img.tile_count[(size_t)t * EAGS_CTR_STRIDE] = start;   // the counter becomes the scatter cursor
+                img.tile_max[t] = 0u;
+                if (c[k] > EAGS_SORT_SMALL_CAP) {
+                    unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
+                    img.big_list[pos] = (unsigned)t;
+                }
             }
+            start += c[k];
         }
         __syncthreads();
-        if (tid == SCAN_THREADS - 1) s_carry = start + c;
+        if (tid == SCAN_THREADS - 1) s_carry = start;
         __syncthreads();
     }
     if (tid == 0) {
