@@ -388,7 +388,27 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
             dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
             ms_e = float(t_e[0])
         eager = {"value": world * 1e3 / ms_e, "unit": UNIT, "ms_per_step": ms_e, "steps": n_e,
-                 "note": "the same step issued eagerly through Python every iteration (sync_mode optimistic)"}
+                 "note": "the DROP-IN number: the same step issued eagerly through Python every iteration, no caller "
+                         "change (sync_mode optimistic: the host waits for the key count of every forward, as upstream does)"}
+        if world == 1:
+            # opt-in sync mode "nosync": the host never waits for the key count (capacity from the high-water
+            # mark, an overflow raises on the next call) -- one call to rz.set_sync_mode, otherwise unchanged
+            prev_mode = rz.get_sync_mode()
+            rz.set_sync_mode("nosync")
+            try:
+                for _ in range(5):
+                    step(devt)
+                evs_n = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_e)]
+                for a, b in evs_n:
+                    flush.zero_()
+                    a.record()
+                    step(devt)
+                    b.record()
+                torch.cuda.synchronize()
+                ms_n = sum(a.elapsed_time(b) for a, b in evs_n) / n_e
+                eager["nosync"] = {"value": 1e3 / ms_n, "unit": UNIT, "ms_per_step": ms_n}
+            finally:
+                rz.set_sync_mode(prev_mode)
     # ---- e2e: host (pinned) inputs, H2D of every Gaussian tensor + D2H of the loss, per step ----
     # Input pipeline: the copy of step i+1's inputs is issued on a copy stream while step i computes
     # (double buffering, as a data loader would); every step's inputs cross PCIe inside the timed

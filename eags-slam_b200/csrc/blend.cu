@@ -234,6 +234,26 @@ blend_fwd_kernel(FwdArgs a) {
                         const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
                         const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
                         if (STATS) st_iters += (lane == 0);
+#ifdef EAGS_FWD_PREDICATED
+                        // branch-free form (if-converted by the compiler: no BSSY / BSYNC pair per splat)
+                        const bool hit = !(power2 > 0.f || alpha < 1.0f / 255.0f);
+                        const float test_T = T * (1.f - alpha);
+                        const bool blend = hit && !(test_T < 0.0001f);
+                        if (hit && !blend) T = -fabsf(T);
+                        if (blend) {
+                            if (STATS) st_pairs++;
+                            const float4 r2 = rec[3 * j + 2];
+                            const float w = alpha * T;
+                            C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
+                            D += r0.w * w;
+                            A += w;
+                            if (VARIANT_B) {
+                                if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                            }
+                            T = test_T;
+                            lastj = j;
+                        }
+#else
                         if (power2 > 0.f || alpha < 1.0f / 255.0f) continue;
                         const float test_T = T * (1.f - alpha);
                         if (test_T < 0.0001f) { T = -fabsf(T); continue; }
@@ -248,6 +268,7 @@ blend_fwd_kernel(FwdArgs a) {
                         }
                         T = test_T;
                         lastj = j;
+#endif
                     }
                 }
                 if (lastj >= 0) last = (unsigned)(base + lastj + 1);
@@ -498,7 +519,9 @@ blend_bwd_kernel(BwdArgs a) {
                         const bool active = (base + j < last_contributor) && (power2 <= 0.f) &&
                                             (alpha >= 1.0f / 255.0f);
                         if (STATS) { st_iters += (lane == 0); st_pairs += active; }
+#ifndef EAGS_BWD_NO_ANY_SKIP
                         if (!__any_sync(FULL, active)) continue;   // warp-uniform
+#endif
                         float gG = 0.f, w = 0.f;
                         if (active) {
                             const float4 r2 = rec[3 * j + 2];
