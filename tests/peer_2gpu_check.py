@@ -164,8 +164,51 @@ for it in range(2):
         for k in pa:
             pb[k].copy_(pa[k])
 assert ex.error_flag() == 0
+
+# the fused owner-side optimiser (eags_peer_adam_step) through ShardedMapper on real ranks: xyz / scaling /
+# rotation / opacity live in the exchange and are stepped inside it; the SH features go through NCCL + SGD.
+# Reference: the pure-NCCL mapper with torch Adam on identical replicas (eps 1e-8, no isotropic term).
+from eags_raster.peer import PeerAdam  # noqa: E402
+
+LR = dict(xyz=1e-4, scaling=5e-3, rotation=1e-3, opacity=5e-2)
+ex3 = PeerGradExchange(P, dev)
+adam = PeerAdam(ex3, lr=LR, eps=1e-8, isotropic_weight=0.0)
+pc = make_params()
+adam.load(pc["xyz"].detach(), pc["scaling"].detach(), pc["rotation"].detach(), pc["opacity"].detach())
+feat_c = pc["features"]
+
+
+def fused_loss(v):
+    act = adam.activated()
+    m2d = torch.zeros_like(act["means3D"], requires_grad=True)
+    color, depth, alpha, radii = rasters[v](means3D=act["means3D"], means2D=m2d, opacities=act["opacities"], shs=feat_c,
+                                            colors_precomp=None, scales=act["scales"], rotations=act["rotations"],
+                                            cov3D_precomp=None)
+    return (color - d["gt_color"]).abs().mean() + (depth - d["gt_depth"]).abs().mean()
+
+
+pd_ = make_params()
+od = torch.optim.Adam([{"params": [pd_[k]], "lr": LR[k]} for k in LR] + [{"params": [pd_["features"]], "lr": 0.0}], eps=1e-8)
+mc = sharded.ShardedMapper([feat_c], torch.optim.SGD([feat_c], lr=0.0), exchange=ex3, fused_optimizer=adam, check_every=1)
+md = sharded.ShardedMapper(list(pd_.values()), od)
+for it in range(3):
+    mc.step(views, fused_loss)
+    md.step(views, make_loss(pd_))
+    torch.cuda.synchronize()
+    for k, lr in LR.items():
+        a_, b_ = adam.params()[k], pd_[k].detach()
+        close = ((a_ - b_).abs() <= 2e-2 * lr + 1e-6 * b_.abs()).float().mean()
+        assert float(close) >= 0.999, ("fused adam", it, k, float(close))
+        c = a_.clone()
+        dist.broadcast(c, src=0)
+        assert torch.equal(c, a_), ("fused adam", it, k, "replicas differ")
+    with torch.no_grad():      # same trajectory for the next step
+        for k in LR:
+            pd_[k].copy_(adam.params()[k])
+assert ex3.error_flag() == 0 and adam.steps_taken() == 3
 dist.barrier()
 if rank == 0:
+    print(f"fused peer Adam ok: 3 steps of {len(views)} views on {world} ranks vs NCCL + torch Adam, replicas bit-identical")
     print(f"sharded mapper ok: {len(views)} views on {world} ranks (2 per rank), peer exchange + NCCL features vs NCCL only")
     print(f"peer exchange ok: world {world}, P {P}, 3 eager steps + 4 graph replays, max rel diff vs NCCL <= 1e-5, replicas bit-identical")
 dist.destroy_process_group()
