@@ -6,7 +6,8 @@
 // by a two-level scheme that moves ~20 B/key through HBM and the rest through shared memory:
 //
 //   K2 tile_scan   : exclusive scan of the per-tile key counts (counted by preprocess_fwd) ->
-//                    `ranges` (== identifyTileRanges output, (0,0) for empty tiles) + scatter cursors.
+//                    `ranges` (== identifyTileRanges output, (0,0) for empty tiles) + scatter cursors;
+//                    one CTA per 1 024 tiles, each re-summing the counts before its own.
 //   K3 duplicate   : (preprocess.cu) scatters (depth_bits << 32 | gaussian) into the tile's bucket.
 //   K4 sort_pack   : one CTA per tile sorts its bucket in shared memory -- an LSD radix sort over the
 //                    depth bits that actually vary inside the tile (8-bit digits, warp-level
@@ -28,77 +29,77 @@ namespace {
 // K2: single-CTA scan over G tile counts (G = 1 200 .. 8 030 for the benchmark shapes).
 // ------------------------------------------------------------------------------------------------
 constexpr int SCAN_THREADS = 1024;
-constexpr int SCAN_PER = 8;   // counters per thread and round: all eight loads are in flight together
 
-// One CTA; thread t of a round owns the SCAN_PER consecutive tiles [base + 8 t, base + 8 t + 8): the counters
-// sit one per 128-byte line, so a round costs ONE memory latency for 8 192 tiles (c2 - c4 need one round)
-// instead of one per 1 024.
+// ceil(G / 1024) CTAs; CTA b owns tiles [1024 b, 1024 b + 1024).  The counters sit one per 128-byte line, so
+// reading them costs one LSU wavefront each: ONE SM scanning all of c4's 8 030 counters (and writing three
+// arrays back) took 25 us of pure load/store issue.  Here every CTA first sums the counters of the tiles
+// BEFORE its own (redundantly: 1024 b loads spread over the CTA, a few per thread) and then scans its own
+// 1 024 -- no inter-CTA dependency, no second kernel.  Because later CTAs still read the counts, the scatter
+// cursor of the exact path goes to word 1 of the tile's line instead of overwriting the count in word 0.
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
     __shared__ unsigned s_warp[SCAN_THREADS / 32];
-    __shared__ unsigned s_carry, s_max;
+    __shared__ unsigned s_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { s_carry = 0; s_max = 0; }
+    const int first = blockIdx.x * SCAN_THREADS;
+    // ---- carry: total of all earlier tiles
+    unsigned pre = 0;
+    for (int t = tid; t < first; t += SCAN_THREADS) pre += img.tile_count[(size_t)t * EAGS_CTR_STRIDE];
+    const int t = first + tid;
+    const unsigned c = (t < img.G) ? img.tile_count[(size_t)t * EAGS_CTR_STRIDE] : 0u;
+    pre = __reduce_add_sync(0xffffffffu, pre);
+    if (lane == 0) s_warp[warp] = pre;
     __syncthreads();
-    for (int base = 0; base < img.G; base += SCAN_THREADS * SCAN_PER) {
-        const int t0 = base + tid * SCAN_PER;
-        unsigned c[SCAN_PER];
+    if (warp == 0) {
+        const unsigned v = __reduce_add_sync(0xffffffffu, s_warp[lane]);
+        if (lane == 0) s_carry = v;
+    }
+    __syncthreads();
+    const unsigned carry = s_carry;
+    __syncthreads();
+    // ---- scan of the CTA's own counters
+    unsigned incl = c;
 #pragma unroll
-        for (int k = 0; k < SCAN_PER; k++)
-            c[k] = (t0 + k < img.G) ? img.tile_count[(size_t)(t0 + k) * EAGS_CTR_STRIDE] : 0u;
-        unsigned mine = 0, mx = 0;
-#pragma unroll
-        for (int k = 0; k < SCAN_PER; k++) { mine += c[k]; mx = max(mx, c[k]); }
-        unsigned incl = mine;
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    const unsigned m = __reduce_max_sync(0xffffffffu, c);
+    if (lane == 0 && m) atomicMax(&img.ctrl->max_tile, m);    // zeroed with the control block
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = s_warp[lane];
+        unsigned wi = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            unsigned n = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += n;
+            unsigned n = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += n;
         }
-        if (lane == 31) s_warp[warp] = incl;
-        {
-            const unsigned m = __reduce_max_sync(0xffffffffu, mx);
-            if (lane == 0 && m) atomicMax(&s_max, m);
-        }
-        __syncthreads();
-        if (warp == 0) {
-            unsigned w = s_warp[lane];
-            unsigned wi = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                unsigned n = __shfl_up_sync(0xffffffffu, wi, o);
-                if (lane >= o) wi += n;
-            }
-            s_warp[lane] = wi - w;   // exclusive prefix of the warp totals
-        }
-        __syncthreads();
-        unsigned start = s_carry + s_warp[warp] + incl - mine;
-#pragma unroll
-        for (int k = 0; k < SCAN_PER; k++) {
-            const int t = t0 + k;
-            if (t < img.G) {
-                img.ranges[t] = c[k] ? make_uint2(start, start + c[k]) : make_uint2(0u, 0u);
-                img.tile_count[(size_t)t * EAGS_CTR_STRIDE] = start;   // the counter becomes the scatter cursor
-                img.tile_max[t] = 0u;
-                if (c[k] > EAGS_SORT_SMALL_CAP) {
-                    unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
-                    img.big_list[pos] = (unsigned)t;
-                }
-            }
-            start += c[k];
-        }
-        __syncthreads();
-        if (tid == SCAN_THREADS - 1) s_carry = start;
-        __syncthreads();
+        s_warp[lane] = wi - w;   // exclusive prefix of the warp totals
     }
-    if (tid == 0) {
-        img.ctrl->num_scanned = s_carry;
-        img.ctrl->max_tile = s_max;
-        if (sticky) {
-            // persistent high-water marks over every forward that was handed this block (CUDA-graph replays:
-            // the owner of the graph looks at it once per frame, an overflow in ANY replay must still show)
+    __syncthreads();
+    const unsigned start = carry + s_warp[warp] + incl - c;
+    if (t < img.G) {
+        img.ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+        img.tile_count[(size_t)t * EAGS_CTR_STRIDE + EAGS_CTR_CURSOR] = start;   // scatter cursor (exact path)
+        img.tile_max[t] = 0u;
+        if (c > EAGS_SORT_SMALL_CAP) {
+            unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
+            img.big_list[pos] = (unsigned)t;
+        }
+    }
+    if (t == img.G - 1) img.ctrl->num_scanned = start + c;
+    if (sticky) {
+        // persistent high-water marks over every forward that was handed this block (CUDA-graph replays: the
+        // owner of the graph looks at it once per frame, an overflow in ANY replay must still show); folded in
+        // by the last CTA to finish, when max_tile is final
+        __threadfence();
+        __syncthreads();
+        if (tid == 0 && atomicAdd(&img.ctrl->work_sort, 1u) == gridDim.x - 1) {
+            __threadfence();
             atomicMax(&sticky->num_rendered, img.ctrl->num_rendered);
-            atomicMax(&sticky->max_tile, s_max);
+            atomicMax(&sticky->max_tile, *(volatile unsigned*)&img.ctrl->max_tile);
             atomicOr(&sticky->bucket_overflow, img.ctrl->bucket_overflow);
         }
     }
@@ -598,7 +599,7 @@ sort_pack_big_kernel(ImagePtrs img, unsigned long long* __restrict__ unsorted, l
 }  // namespace
 
 int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s) {
-    tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(img, sticky);
+    tile_scan_kernel<<<(img.G + SCAN_THREADS - 1) / SCAN_THREADS, SCAN_THREADS, 0, s>>>(img, sticky);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -15,9 +15,9 @@
 //
 //   image state  (per tile / per pixel)
 //     ctrl          Ctrl        counters, zeroed at the start of every forward
-//     tile_count    u32[G*32]   keys per tile, one counter per 128-byte line (zeroed with ctrl; RED
-//                               atomics in preprocess_fwd); tile_scan turns it into the scatter
-//                               cursor that duplicate advances with ATOM
+//     tile_count    u32[G*32]   keys per tile, one counter per 128-byte line (word 0; zeroed with ctrl; RED
+//                               atomics in preprocess_fwd); tile_scan leaves the tile's scatter cursor
+//                               in word 1 of the same line, which duplicate advances with ATOM
 //     ranges        uint2[G]    [start, end) of each tile in the sorted list
 //     big_list      u32[G]      tiles whose list does not fit the small sort CTA
 //     tile_max      u32[G]      max n_contrib over the tile's pixels (bounds the backward walk)
@@ -36,6 +36,7 @@
 #include <stdint.h>
 
 #define EAGS_TILE 16
+#define EAGS_CTR_CURSOR 1           // word of a tile's counter line that holds its scatter cursor (exact path)
 #define EAGS_CTR_STRIDE 32          // per-tile counters live one per 128-byte line: the L2 atomic unit
                                    // serialises RED/ATOM traffic per line, 38 hot lines cost 60 us at c2
 #define EAGS_SORT_SMALL_CAP 2048   // keys a 256-thread sort CTA holds in shared memory

@@ -316,7 +316,7 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, GeomP
     const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)i;
     for (int y = y0; y < y1; y++)
         for (int x = x0; x < x1; x++) {
-            unsigned slot = atomicAdd(&tile_cursor[(size_t)(y * gx + x) * EAGS_CTR_STRIDE], 1u);
+            unsigned slot = atomicAdd(&tile_cursor[(size_t)(y * gx + x) * EAGS_CTR_STRIDE + EAGS_CTR_CURSOR], 1u);
             unsorted[slot] = key;
         }
 }

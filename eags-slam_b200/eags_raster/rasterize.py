@@ -552,6 +552,16 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
 
 def state_array(state: RasterState, name: str) -> torch.Tensor:
     """Copy one named array out of the opaque state buffers (parity tests / debugging)."""
+    if name in ("xy", "rgbd", "conic_opacity"):
+        # views derived from the per-Gaussian splat records (the conic is stored pre-scaled for the blend
+        # kernels: undo the -log2(e)/2, -log2(e), -log2(e)/2 factors)
+        rec = state_array(state, "splat_rec")
+        if name == "xy":
+            return rec[:, 0:2].contiguous()
+        if name == "rgbd":
+            return torch.cat([rec[:, 8:11], rec[:, 3:4]], dim=1).contiguous()
+        L = 1.4426950408889634
+        return torch.stack([rec[:, 4] / (-0.5 * L), rec[:, 5] / (-L), rec[:, 6] / (-0.5 * L), rec[:, 7]], dim=1)
     lib = _lib.load()
     ptr, cnt, eb = C.c_void_p(0), C.c_int64(0), C.c_int32(0)
     _lib.check(lib.eags_state_view(name.encode(), state.P, state.W, state.H, state.capacity,
@@ -565,16 +575,6 @@ def state_array(state: RasterState, name: str) -> torch.Tensor:
             break
     else:
         raise RuntimeError("state array outside the state buffers")
-    if name in ("xy", "rgbd", "conic_opacity"):
-        # views derived from the per-Gaussian splat records (the conic is stored pre-scaled for the blend
-        # kernels: undo the -log2(e)/2, -log2(e), -log2(e)/2 factors)
-        rec = state_array(state, "splat_rec")
-        if name == "xy":
-            return rec[:, 0:2].contiguous()
-        if name == "rgbd":
-            return torch.cat([rec[:, 8:11], rec[:, 3:4]], dim=1).contiguous()
-        L = 1.4426950408889634
-        return torch.stack([rec[:, 4] / (-0.5 * L), rec[:, 5] / (-L), rec[:, 6] / (-0.5 * L), rec[:, 7]], dim=1)
     dt = {"splat_rec": (torch.float32, (-1, 12)), "tiles_touched": (torch.int32, (-1,)),
           "clamped": (torch.uint8, (-1,)), "tile_count": (torch.int32, (-1,)),
           "ranges": (torch.int32, (-1, 2)), "tile_max_contrib": (torch.int32, (-1,)),
