@@ -1,0 +1,8 @@
+set -x
+timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -12 > gpurun_out/r2g_pytest.txt
+timeout 300 python profiles/kernel_ab.py --workloads c2,c3,c4 --opts radix_sort=2 --orders random,tile --reps 15 > gpurun_out/r2g_ab.txt 2>&1
+timeout 600 python bench.py --steps 100 --warmup 10 > gpurun_out/r2g_bench.json 2> gpurun_out/r2g_bench.err
+timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu --no-mapping > gpurun_out/plain.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r2g_launches_bench.csv python bench.py --steps 3 --warmup 3 --no-cpu --no-mapping > gpurun_out/ncu1.log 2>&1
+timeout 300 python profiles/run_step.py --iters 3 > /dev/null 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:'blend|sort_pack_small|preprocess|tile_scan' --launch-skip 12 -c 6 -o gpurun_out/r2g_full -f python profiles/run_step.py --iters 3 > gpurun_out/r2g_ncu.log 2>&1
+timeout 120 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r2g_ref.json 2>/dev/null
+cat gpurun_out/r2g_pytest.txt gpurun_out/r2g_ab.txt; tail -c 300 gpurun_out/r2g_bench.json; tail -2 gpurun_out/r2g_ncu.log
