@@ -134,3 +134,38 @@ def test_depth_tie_runs(P, run):
     # the view transform must keep the ties exact: z is copied, the camera is the identity
     assert len(np.unique(o["depths"][o["radii"] > 0])) <= (P + run - 1) // run
     _all_variants(cam, sc, o)
+
+
+def test_tile_order_changes_no_rendered_value():
+    """eags_raster.reorder.tile_order: the same Gaussians stored by projected tile render the same image
+    bit for bit (the blend order inside a tile is (depth, index); no exact depth ties in this scene), and the
+    radii / gradients are the permuted originals."""
+    from eags_raster import reorder
+    from gaussian_rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda")
+    sc = scene.make_scene("c1", P=80_000, seed=13)
+    cam = scene.workload_camera("c1", w2c=scene.rot_xy(2, 3))
+    s = GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=torch.zeros(3, device=dev),
+        scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev), projmatrix=cam.projmatrix.to(dev), sh_degree=0,
+        campos=cam.campos.to(dev), prefiltered=False, debug=False)
+    keys = ("means3D", "scales", "rotations", "opacities", "shs")
+    a = {k: sc[k].to(dev) for k in keys}
+    perm = reorder.tile_order(a["means3D"], s)
+    assert sorted(perm.tolist()) == list(range(80_000))
+    b = dict(zip(keys, reorder.apply_order(perm, [a[k] for k in keys])))
+
+    def render(t):
+        leaf = {k: v.clone().requires_grad_(True) for k, v in t.items()}
+        color, depth, alpha, radii = GaussianRasterizer(raster_settings=s)(
+            means3D=leaf["means3D"], means2D=torch.zeros_like(leaf["means3D"], requires_grad=True),
+            opacities=leaf["opacities"], shs=leaf["shs"], colors_precomp=None, scales=leaf["scales"],
+            rotations=leaf["rotations"], cov3D_precomp=None)
+        (color.sum() + depth.sum()).backward()
+        return color, depth, alpha, radii, leaf["means3D"].grad
+
+    ca, da, aa, ra, ga = render(a)
+    cb, db, ab, rb, gb = render(b)
+    assert torch.equal(ca, cb) and torch.equal(da, db) and torch.equal(aa, ab)
+    assert torch.equal(ra[perm], rb)
+    assert float((ga[perm] - gb).abs().max()) <= 1e-5 * float(ga.abs().max())
