@@ -504,20 +504,34 @@ struct PackArgs {
     unsigned long long* keys;   // nullable
 };
 
-// entry k of the sorted list is (depth_bits, gaussian) = get(k)
+// entry k of the sorted list is (depth_bits, gaussian) = get(k).  Two entries per thread and round: all six
+// 16-byte gathers are requested before the first store, so a round costs one L2 latency instead of two
+// (the compiler cannot hoist the second entry's loads above the first one's stores by itself).
 template <int THREADS, typename Get>
 __device__ __forceinline__ void pack_sorted(Get get, int n, unsigned start, unsigned tile, const PackArgs& a) {
-    for (int k = threadIdx.x; k < n; k += THREADS) {
+    for (int k = threadIdx.x; k < n; k += 2 * THREADS) {
+        const int k2 = k + THREADS;
+        const bool two = k2 < n;
         const uint2 e = get(k);
-        const unsigned idx = e.y;
-        const float4* __restrict__ g = a.splat_rec + (size_t)3 * idx;   // 48 contiguous bytes
-        const float4 g0 = g[0], g1 = g[1], g2 = g[2];
+        const uint2 f = two ? get(k2) : e;
+        const float4* __restrict__ g = a.splat_rec + (size_t)3 * e.y;   // 48 contiguous bytes per Gaussian
+        const float4* __restrict__ h = a.splat_rec + (size_t)3 * f.y;
+        const float4 g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
+        const float4 h0 = __ldg(h), h1 = __ldg(h + 1), h2 = __ldg(h + 2);
         const size_t o = (size_t)start + k;
-        a.point_list[o] = idx;
+        a.point_list[o] = e.y;
         a.records[3 * o + 0] = g0;
         a.records[3 * o + 1] = g1;
         a.records[3 * o + 2] = g2;
         if (a.keys) a.keys[o] = ((unsigned long long)tile << 32) | e.x;
+        if (two) {
+            const size_t o2 = (size_t)start + k2;
+            a.point_list[o2] = f.y;
+            a.records[3 * o2 + 0] = h0;
+            a.records[3 * o2 + 1] = h1;
+            a.records[3 * o2 + 2] = h2;
+            if (a.keys) a.keys[o2] = ((unsigned long long)tile << 32) | f.x;
+        }
     }
 }
 
