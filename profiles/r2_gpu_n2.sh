@@ -1,6 +1,7 @@
 # two GPUs of one box (gpurun --gpus 2): multi-rank correctness + the N = 2 points of the scaling curves
 set -x
 N=${1:-2}
+timeout 600 python -m pytest tests/test_gpu_binning_variants.py tests/test_gpu_parity.py -q -m gpu -x 2>&1 | tail -3 > gpurun_out/r2n${1:-2}_sanity.txt; cat gpurun_out/r2n${1:-2}_sanity.txt
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
 timeout 300 $TR tests/peer_2gpu_check.py > gpurun_out/r2n${N}_peer_check.txt 2>&1; tail -4 gpurun_out/r2n${N}_peer_check.txt
 timeout 600 python -m pytest tests/test_gpu_peer.py tests/test_handoff.py -q -m gpu 2>&1 | tail -5 > gpurun_out/r2n${N}_pytest.txt; cat gpurun_out/r2n${N}_pytest.txt
