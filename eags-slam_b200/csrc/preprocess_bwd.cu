@@ -60,7 +60,22 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
     const volatile float* F = s_cam_store + 16;
 #define WM(i, k) V[(k) * 4 + (i)]
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
-    const bool vis = i < a.P && b.radii[i] > 0;
+    // every input of the Gaussian is requested before its radius is known: one DRAM latency per thread
+    // instead of two (the ~10 % culled Gaussians cost a few wasted sectors)
+    const bool have_sr = !a.cov3D_precomp;      // kernel-uniform
+    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga, gc = ga, q_in = ga;
+    float p_in[3] = {0.f, 0.f, 0.f}, sc_in[3] = {0.f, 0.f, 0.f};
+    int radius = 0;
+    if (i < a.P) {
+        radius = b.radii[i];
+        ga = b.grad_acc[(size_t)3 * i]; gb = b.grad_acc[(size_t)3 * i + 1]; gc = b.grad_acc[(size_t)3 * i + 2];
+        p_in[0] = a.means3D[(size_t)3 * i]; p_in[1] = a.means3D[(size_t)3 * i + 1]; p_in[2] = a.means3D[(size_t)3 * i + 2];
+        if (have_sr) {
+            sc_in[0] = a.scales[(size_t)3 * i]; sc_in[1] = a.scales[(size_t)3 * i + 1]; sc_in[2] = a.scales[(size_t)3 * i + 2];
+            q_in = *reinterpret_cast<const float4*>(a.rotations + (size_t)4 * i);
+        }
+    }
+    const bool vis = radius > 0;
     float* sh_row = nullptr;
     unsigned sh_rows = 0;
     if constexpr (WIDE) {
@@ -83,21 +98,20 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
         float p[3] = {0.f, 0.f, 0.f};
         unsigned clamped = 0;
         if (vis) {
-            const float4 ga = b.grad_acc[(size_t)3 * i], gb = b.grad_acc[(size_t)3 * i + 1],
-                         gc = b.grad_acc[(size_t)3 * i + 2];
             g2x = ga.x; g2y = ga.y;
             const float gxx = ga.z, gxy = ga.w, gyy = gb.x;
             dop = gb.y;
             dcol[0] = gb.z; dcol[1] = gb.w; dcol[2] = gc.x;
             const float dd = gc.y;
             clamped = b.clamped[i];
-            p[0] = a.means3D[(size_t)3 * i]; p[1] = a.means3D[(size_t)3 * i + 1]; p[2] = a.means3D[(size_t)3 * i + 2];
+            p[0] = p_in[0]; p[1] = p_in[1]; p[2] = p_in[2];
             float pv[3];
             pv[0] = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
             pv[1] = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
             pv[2] = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
             float c6[6];
-            load_cov6(a, i, c6);
+            if (have_sr) cov3d_from_scale_rot(sc_in, a.scale_modifier, q_in, c6);
+            else load_cov6(a, i, c6);
             const float fx = (float)a.W / (2.f * a.tanfovx);
             const float fy = (float)a.H / (2.f * a.tanfovy);
             Ewa e;
@@ -253,12 +267,11 @@ preprocess_bwd_kernel(PreArgs a, BwdArgs b) {
             for (int k = 0; k < 3; k++) dm[k] = dmean_cov[k] + dmean_proj[k] + dmean_dep[k] + dmean_sh[k];
             // Sigma -> scale, rotation
             if (!a.cov3D_precomp && (b.dscales || b.drotations)) {
-                const float4 q = *reinterpret_cast<const float4*>(a.rotations + (size_t)4 * i);
+                const float4 q = q_in;
                 float R[3][3];
                 quat_to_R(q, R);
-                const float s[3] = {a.scale_modifier * a.scales[(size_t)3 * i],
-                                    a.scale_modifier * a.scales[(size_t)3 * i + 1],
-                                    a.scale_modifier * a.scales[(size_t)3 * i + 2]};
+                const float s[3] = {a.scale_modifier * sc_in[0], a.scale_modifier * sc_in[1],
+                                    a.scale_modifier * sc_in[2]};
                 const float Dm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
                                         {0.5f * dS[1], dS[3], 0.5f * dS[4]},
                                         {0.5f * dS[2], 0.5f * dS[4], dS[5]}};

@@ -108,7 +108,8 @@ for sid in range(a.submaps):
         torch.cuda.synchronize()
         dist.send(torch.ones(1, device=dev), dst=0)
         owned[sid] = got
-        dist.recv(torch.zeros(1, device=dev), src=0)  # the checkpoint file is complete
+        dist.recv(torch.zeros(1, device=dev), src=0)  # the checkpoint file is complete ...
+        torch.cuda.synchronize()                      # ... once the (stream-ordered) NCCL receive has really landed
         t0 = time.perf_counter()
         back = torch.load(os.path.join(tmp, f"{str(sid).zfill(6)}.ckpt"), map_location=dev, weights_only=False)
         torch.cuda.synchronize()
