@@ -201,11 +201,13 @@ if rank == 0:
            "iterations_per_s": a.submaps * a.views * a.iters / ms * 1e3, "ms_per_iteration_per_gpu": ms / max(total_it, 1),
            "collective": "none (replicas only)",
            "handoff": {"submap_bytes": bytes_sm,
-                       "send_recv_submap_ms_median": med(t_hand),
+                       "send_recv_submap_ms_median": med(t_hand), "send_recv_submap_ms_min": (min(t_hand) * 1e3) if t_hand else None,
+                       "send_recv_submap_ms_all": [round(x * 1e3, 3) for x in t_hand],
                        "disk_torch_save_ms_median": med(t_disk_save), "disk_torch_load_ms_median": ld,
                        "mailbox_put_other_device_ms": [x * 1e3 for x in t_box] or None,
                        "note": "send/recv: rank 0 -> registering rank over NCCL P2P incl. the pickled header and the "
-                               "consumer's acknowledgement; disk: the reference's torch.save + torch.load(map_location) of the "
+                               "consumer's acknowledgement (the FIRST send to each peer also creates the NCCL P2P channel, "
+                               "hundreds of ms: see _all); disk: the reference's torch.save + torch.load(map_location) of the "
                                "same dictionary through a temp directory; mailbox: one process, cuda:0 -> another device"}}
     print(json.dumps(res))
     if a.json:
