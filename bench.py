@@ -867,6 +867,20 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
     ms, launches, gi = time_mapping(job, steps, warmup, flush, use_graph, barrier)
     e2e_ms, h2d_rank = mapping_e2e(job, gi, min(steps, 50), barrier)
     clocks = sampler.stop() if rank == 0 else None
+    # where the step's device time goes: a few eager steps with the library's per-launcher CUDA-event spans on
+    # (every rank runs them -- the step is collective; rank 0 reports its own)
+    from eags_raster import _lib as _l
+    spans_ms, n_sp = {}, 3
+    _l.set_option("kernel_timing", 1)
+    try:
+        for _ in range(n_sp):
+            job.step()
+            torch.cuda.synchronize()
+            for name, t_ in _l.kernel_times():
+                spans_ms[name] = spans_ms.get(name, 0.0) + t_ / n_sp
+    finally:
+        _l.set_option("kernel_timing", 0)
+    barrier()
     err_after = job.ex.error_flag() if fused else 0
     finite = bool(all(torch.isfinite(v).all() for v in job.params().values()))
     if world > 1:
@@ -918,6 +932,7 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
                             "host memory every step, two steps ahead on a copy stream; the loss is read back every step"},
         "gpu_launches": int(round(launches * steps)), "gpu_launches_per_step": launches,
         "exchange_check": chk, "n1_same_job": n1, "clocks": clocks,
+        "kernels_ms_per_step_rank0": {k: round(v, 4) for k, v in spans_ms.items()},
     }
 
 

@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "kernels.h"
@@ -22,10 +23,16 @@ std::atomic<unsigned long long> g_launches{0};
 // product path never records events.
 std::atomic<int> g_opt_timing{0};
 struct TimedSpan { const char* name; cudaEvent_t beg, end; };
-thread_local std::vector<TimedSpan> g_spans;
-thread_local std::vector<cudaEvent_t> g_event_pool;
+// process-wide (mutex-guarded), not thread-local: autograd runs the backward launchers on its own device
+// thread, and the caller of eags_kernel_times() wants those spans too
+std::mutex g_span_mu;
+std::vector<TimedSpan> g_spans;
+std::vector<cudaEvent_t> g_event_pool;
 cudaEvent_t take_event() {
-    if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    {
+        std::lock_guard<std::mutex> lk(g_span_mu);
+        if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    }
     cudaEvent_t e = nullptr;
     cudaEventCreate(&e);
     return e;
@@ -35,7 +42,13 @@ struct ScopedSpan {
     ScopedSpan(const char* name, cudaStream_t st) : s(st), on(g_opt_timing.load() != 0) {
         if (on) { span.name = name; span.beg = take_event(); span.end = take_event(); cudaEventRecord(span.beg, s); }
     }
-    ~ScopedSpan() { if (on) { cudaEventRecord(span.end, s); g_spans.push_back(span); } }
+    ~ScopedSpan() {
+        if (on) {
+            cudaEventRecord(span.end, s);
+            std::lock_guard<std::mutex> lk(g_span_mu);
+            g_spans.push_back(span);
+        }
+    }
 };
 
 int fail(int code, const char* what) {
@@ -110,16 +123,20 @@ int eags_get_option(const char* name, int32_t* value) {
 }
 
 int eags_kernel_times(int32_t max_spans, const char** names, float* ms) {
+    std::vector<TimedSpan> spans;
+    {
+        std::lock_guard<std::mutex> lk(g_span_mu);
+        spans.swap(g_spans);
+    }
     int n = 0;
-    for (TimedSpan& sp : g_spans) {
+    for (TimedSpan& sp : spans) {
         float t = 0.f;
         cudaEventSynchronize(sp.end);
         cudaEventElapsedTime(&t, sp.beg, sp.end);
         if (n < max_spans && names && ms) { names[n] = sp.name; ms[n] = t; n++; }
-        g_event_pool.push_back(sp.beg);
-        g_event_pool.push_back(sp.end);
     }
-    g_spans.clear();
+    std::lock_guard<std::mutex> lk(g_span_mu);
+    for (TimedSpan& sp : spans) { g_event_pool.push_back(sp.beg); g_event_pool.push_back(sp.end); }
     return n;
 }
 

@@ -362,7 +362,7 @@ int eags_set_option(const char* name, int32_t value);
 int eags_get_option(const char* name, int32_t* value);
 
 /* Measurement hook (bench.py's live per-kernel roofline): waits for and returns the spans recorded
- * by the calling thread since the last call -- names[i] is a static string ("preprocess_fwd",
+ * by ANY thread of the process since the last call (autograd runs the backward on its own thread) -- names[i] is a static string ("preprocess_fwd",
  * "tile_scan", "duplicate", "sort_pack", "blend_fwd", "blend_bwd", "preprocess_bwd"), ms[i] the
  * device time of that launcher.  Returns the number of spans written (<= max_spans). */
 int eags_kernel_times(int32_t max_spans, const char** names, float* ms);
