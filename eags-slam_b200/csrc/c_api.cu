@@ -336,6 +336,18 @@ int eags_pose_se3_update(float* theta, float* rho, float* viewmatrix, const floa
     return 0;
 }
 
+int eags_pose_adam_se3_update(const float* grad_theta, const float* grad_rho, float* state13, float lr_rot,
+                              float lr_trans, float beta1, float beta2, float eps, float* viewmatrix,
+                              const float* projmatrix_raw, float* projmatrix_out, float* campos_out, float* tau_norm,
+                              void* stream) {
+    if (!grad_theta || !grad_rho || !state13 || !viewmatrix || !projmatrix_raw || !projmatrix_out || !campos_out)
+        return fail(EAGS_ERR_INVALID, "eags_pose_adam_se3_update: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_pose_adam_se3(grad_theta, grad_rho, state13, lr_rot, lr_trans, beta1, beta2, eps, viewmatrix,
+                                      projmatrix_raw, projmatrix_out, campos_out, tau_norm, s), "pose_adam_se3");
+    return 0;
+}
+
 size_t eags_image_l1_scratch_bytes(int32_t W, int32_t H) { return image_l1_scratch_bytes(W, H); }
 
 int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
@@ -347,7 +359,7 @@ int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth,
     cudaStream_t s = (cudaStream_t)stream;
     CHECK_LAUNCH(launch_image_l1_fwd(in->width, in->height, in->soft_alpha, in->mask_color, in->norm_mode,
                                      in->eps, in->color, in->depth, in->alpha, in->gt_color, in->gt_depth,
-                                     in->mask, g_color, g_depth, g_alpha, scratch, sums4, s),
+                                     in->mask, in->mask_depth, in->alpha_min, g_color, g_depth, g_alpha, scratch, sums4, s),
                  "image_l1_fwd");
     return 0;
 }

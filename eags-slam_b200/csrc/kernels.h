@@ -86,8 +86,8 @@ int launch_preprocess_bwd(const EagsView& v, const EagsGaussians& g, const int32
 size_t image_l1_scratch_bytes(int W, int H);
 int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
                         const float* color, const float* depth, const float* alpha, const float* gt_color,
-                        const float* gt_depth, const uint8_t* mask, float* g_color, float* g_depth,
-                        float* g_alpha, void* scratch, float* out4, cudaStream_t s);
+                        const float* gt_depth, const uint8_t* mask, const uint8_t* mask_depth, float alpha_min,
+                        float* g_color, float* g_depth, float* g_alpha, void* scratch, float* out4, cudaStream_t s);
 int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
                           float* g_color, float* g_depth, float* g_alpha, cudaStream_t s);
 
@@ -100,6 +100,9 @@ int launch_pose_chain(const float* q, const float* t, const float* view, const f
 
 int launch_pose_se3_update(float* theta, float* rho, float* view, const float* proj_raw, float* proj_out,
                            float* campos_out, float* tau_norm, cudaStream_t s);
+int launch_pose_adam_se3(const float* g_theta, const float* g_rho, float* state, float lr_rot, float lr_trans,
+                         float beta1, float beta2, float eps, float* view, const float* proj_raw, float* proj_out,
+                         float* campos_out, float* tau_norm, cudaStream_t s);
 
 // knn.cu
 size_t neighbors_workspace_bytes(long long n_ref);

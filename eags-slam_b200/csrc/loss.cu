@@ -28,6 +28,8 @@ struct LossArgs {
     const float* gt_color; // (3,N)
     const float* gt_depth; // (N)
     const uint8_t* mask;   // (N) or NULL (all valid)
+    const uint8_t* mask_depth;   // (N) or NULL (= mask)
+    float alpha_min;       // soft_alpha == 2: opacity threshold of the depth term
     float* g_color;        // (3,N) raw gradient
     float* g_depth;        // (N)
     float* g_alpha;        // (N) or NULL
@@ -44,9 +46,14 @@ image_l1_fwd_kernel(LossArgs a) {
     for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < a.N; p += gridDim.x * LOSS_THREADS) {
         const float m = a.mask ? (a.mask[p] ? 1.f : 0.f) : 1.f;
         const float al = a.alpha ? a.alpha[p] : 1.f;
-        const float w = a.soft_alpha ? al * al * al : 1.f;
-        const float wc = w * ((a.mask_color || !a.soft_alpha) ? m : 1.f);   // tracker.py:118-125
-        const float wd = w * m;
+        const float md = a.mask_depth ? (a.mask_depth[p] ? 1.f : 0.f) : m;
+        const float w = a.soft_alpha == 1 ? al * al * al : 1.f;
+        float wc = w * ((a.mask_color || !a.soft_alpha) ? m : 1.f);   // tracker.py:118-125
+        float wd = w * md;
+        if (a.soft_alpha == 2) {   // registration loss, src/gsr/loss.py:66-95
+            wc = al * m;
+            wd = md * (al > a.alpha_min ? 1.f : 0.f);
+        }
         float lc_sum = 0.f;
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -54,22 +61,22 @@ image_l1_fwd_kernel(LossArgs a) {
             const float l = (fabsf(d) + a.eps) * wc;
             lc_sum += fabsf(d) + a.eps;
             s_c += l;
-            n_c += (a.norm_mode == 0) ? (l > 0.f ? 1.f : 0.f) : m;
+            n_c += (a.norm_mode == 0) ? (l > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? m : 1.f);
             a.g_color[(size_t)c * a.N + p] = sgn(d) * wc;
         }
         const float dd = a.depth[p] - a.gt_depth[p];
         const float ld0 = fabsf(dd) + a.eps;
         const float ld = ld0 * wd;
         s_d += ld;
-        n_d += (a.norm_mode == 0) ? (ld > 0.f ? 1.f : 0.f) : m;
+        n_d += (a.norm_mode == 0) ? (ld > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? md : 1.f);
         a.g_depth[p] = sgn(dd) * wd;
         if (a.g_alpha) {
             // d(alpha^3)/dalpha = 3 alpha^2, applied to the unweighted loss terms it multiplies; the
             // colour and depth parts are scaled by different factors later, so they are kept apart
             // in the two halves of a float2-like pair: colour part here, depth part in slot N + p.
-            const float d3 = a.soft_alpha ? 3.f * al * al : 0.f;
-            a.g_alpha[p] = d3 * lc_sum * ((a.mask_color) ? m : 1.f);
-            a.g_alpha[(size_t)a.N + p] = d3 * ld0 * m;
+            const float d3 = a.soft_alpha == 1 ? 3.f * al * al : 0.f;
+            a.g_alpha[p] = a.soft_alpha == 2 ? lc_sum * m : d3 * lc_sum * ((a.mask_color) ? m : 1.f);
+            a.g_alpha[(size_t)a.N + p] = a.soft_alpha == 2 ? 0.f : d3 * ld0 * md;   // (alpha > min) has no gradient
         }
     }
     // block reduction (fixed order inside the block), then a fixed-order pass over the partials
@@ -146,12 +153,13 @@ size_t image_l1_scratch_bytes(int W, int H) {
 
 int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
                         const float* color, const float* depth, const float* alpha, const float* gt_color,
-                        const float* gt_depth, const uint8_t* mask, float* g_color, float* g_depth,
+                        const float* gt_depth, const uint8_t* mask, const uint8_t* mask_depth, float alpha_min,
+                        float* g_color, float* g_depth,
                         float* g_alpha, void* scratch, float* out4, cudaStream_t s) {
     LossArgs a;
     a.N = W * H; a.soft_alpha = soft_alpha; a.mask_color = mask_color; a.norm_mode = norm_mode; a.eps = eps;
     a.color = color; a.depth = depth; a.alpha = alpha; a.gt_color = gt_color; a.gt_depth = gt_depth;
-    a.mask = mask; a.g_color = g_color; a.g_depth = g_depth; a.g_alpha = g_alpha;
+    a.mask = mask; a.mask_depth = mask_depth; a.alpha_min = alpha_min; a.g_color = g_color; a.g_depth = g_depth; a.g_alpha = g_alpha;
     a.ticket = (unsigned*)scratch;
     a.partial = (double*)((char*)scratch + 256);
     a.out = out4;

@@ -107,12 +107,9 @@ __global__ void pose_chain_kernel(const float* __restrict__ q, const float* __re
 //   w2c <- SE3_exp([rho, theta]) w2c  (pose_utils.py:40-74: Rodrigues rotation, V(theta) rho, the small-angle
 //   series below 1e-5), viewmatrix = w2c^T, projmatrix = viewmatrix projmatrix_raw, campos = -R^T t,
 //   theta, rho <- 0.  One thread; replaces ~25 tiny torch kernels and the host round trip per iteration.
-__global__ void pose_se3_update_kernel(float* __restrict__ theta, float* __restrict__ rho,
-                                       float* __restrict__ view, const float* __restrict__ proj_raw,
-                                       float* __restrict__ proj_out, float* __restrict__ campos_out,
-                                       float* __restrict__ tau_norm) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const float th[3] = {theta[0], theta[1], theta[2]}, rh[3] = {rho[0], rho[1], rho[2]};
+__device__ void se3_apply(const float th[3], const float rh[3], float* __restrict__ view,
+                          const float* __restrict__ proj_raw, float* __restrict__ proj_out,
+                          float* __restrict__ campos_out, float* __restrict__ tau_norm) {
     const float W[3][3] = {{0.f, -th[2], th[1]}, {th[2], 0.f, -th[0]}, {-th[1], th[0], 0.f}};
     float W2[3][3];
     for (int i = 0; i < 3; i++)
@@ -161,7 +158,44 @@ __global__ void pose_se3_update_kernel(float* __restrict__ theta, float* __restr
     for (int k = 0; k < 16; k++) view[k] = Vn[k];
     for (int i = 0; i < 3; i++) campos_out[i] = -(Rn[0][i] * tn[0] + Rn[1][i] * tn[1] + Rn[2][i] * tn[2]);
     if (tau_norm) *tau_norm = sqrtf(angle * angle + rh[0] * rh[0] + rh[1] * rh[1] + rh[2] * rh[2]);
+}
+
+__global__ void pose_se3_update_kernel(float* __restrict__ theta, float* __restrict__ rho,
+                                       float* __restrict__ view, const float* __restrict__ proj_raw,
+                                       float* __restrict__ proj_out, float* __restrict__ campos_out,
+                                       float* __restrict__ tau_norm) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const float th[3] = {theta[0], theta[1], theta[2]}, rh[3] = {rho[0], rho[1], rho[2]};
+    se3_apply(th, rh, view, proj_raw, proj_out, campos_out, tau_norm);
     for (int i = 0; i < 3; i++) { theta[i] = 0.f; rho[i] = 0.f; }
+}
+
+// K14 pose_adam_se3: the whole optimiser side of one registration iteration (reference src/gsr/solver.py:83-91:
+// optimizer.step() on cam_rot_delta / cam_trans_delta, then update_pose) in one thread.  The two deltas are
+// zero when the step starts (update_pose zeroes them every iteration), so the Adam step IS the delta:
+//   m <- b1 m + (1 - b1) g,  v <- b2 v + (1 - b2) g^2,  tau = -lr (m / (1 - b1^t)) / (sqrt(v / (1 - b2^t)) + eps)
+// (torch.optim.Adam semantics, per-group learning rates: rotation 3 x base, translation base), followed by
+// w2c <- SE3_exp(tau) w2c.  state = {m[6] (theta, rho), v[6], step} as 13 floats, zeroed by the caller.
+__global__ void pose_adam_se3_kernel(const float* __restrict__ g_theta, const float* __restrict__ g_rho,
+                                     float* __restrict__ state, float lr_rot, float lr_trans, float beta1,
+                                     float beta2, float eps, float* __restrict__ view,
+                                     const float* __restrict__ proj_raw, float* __restrict__ proj_out,
+                                     float* __restrict__ campos_out, float* __restrict__ tau_norm) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const float t = state[12] + 1.f;
+    state[12] = t;
+    const float bc1 = 1.f - powf(beta1, t), bc2 = 1.f - powf(beta2, t);
+    float tau[6];
+    for (int k = 0; k < 6; k++) {
+        const float g = k < 3 ? g_theta[k] : g_rho[k - 3];
+        const float m = beta1 * state[k] + (1.f - beta1) * g;
+        const float v = beta2 * state[6 + k] + (1.f - beta2) * g * g;
+        state[k] = m;
+        state[6 + k] = v;
+        const float lr = k < 3 ? lr_rot : lr_trans;
+        tau[k] = -(lr / bc1) * m / (sqrtf(v) / sqrtf(bc2) + eps);
+    }
+    se3_apply(tau, tau + 3, view, proj_raw, proj_out, campos_out, tau_norm);
 }
 
 }  // namespace
@@ -169,6 +203,14 @@ __global__ void pose_se3_update_kernel(float* __restrict__ theta, float* __restr
 int launch_pose_se3_update(float* theta, float* rho, float* view, const float* proj_raw, float* proj_out,
                            float* campos_out, float* tau_norm, cudaStream_t s) {
     pose_se3_update_kernel<<<1, 32, 0, s>>>(theta, rho, view, proj_raw, proj_out, campos_out, tau_norm);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_pose_adam_se3(const float* g_theta, const float* g_rho, float* state, float lr_rot, float lr_trans,
+                         float beta1, float beta2, float eps, float* view, const float* proj_raw, float* proj_out,
+                         float* campos_out, float* tau_norm, cudaStream_t s) {
+    pose_adam_se3_kernel<<<1, 32, 0, s>>>(g_theta, g_rho, state, lr_rot, lr_trans, beta1, beta2, eps, view, proj_raw,
+                                          proj_out, campos_out, tau_norm);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -61,7 +61,7 @@ class EagsImageL1(C.Structure):
         ("width", C.c_int32), ("height", C.c_int32), ("soft_alpha", C.c_int32), ("mask_color", C.c_int32),
         ("norm_mode", C.c_int32), ("eps", C.c_float),
         ("color", C.c_void_p), ("depth", C.c_void_p), ("alpha", C.c_void_p), ("gt_color", C.c_void_p),
-        ("gt_depth", C.c_void_p), ("mask", C.c_void_p),
+        ("gt_depth", C.c_void_p), ("mask", C.c_void_p), ("mask_depth", C.c_void_p), ("alpha_min", C.c_float),
     ]
 
 
@@ -115,6 +115,9 @@ SIGNATURES = {
     "eags_pose_compose": (C.c_int, [C.c_void_p] * 9),
     "eags_pose_chain": (C.c_int, [C.c_void_p] * 7),
     "eags_pose_se3_update": (C.c_int, [C.c_void_p] * 8),
+    "eags_pose_adam_se3_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
+                                            C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p]),
     "eags_neighbors_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "eags_knn_mean_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "eags_radius_has_neighbor": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_float, C.c_void_p,

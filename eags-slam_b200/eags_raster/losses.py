@@ -31,7 +31,8 @@ def _c(t: torch.Tensor) -> torch.Tensor:
 
 class _ImageL1(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, color, depth, alpha, gt_color, gt_depth, mask, soft_alpha, mask_color, norm_mode, eps):
+    def forward(ctx, color, depth, alpha, gt_color, gt_depth, mask, soft_alpha, mask_color, norm_mode, eps,
+                mask_depth=None, alpha_min=0.0):
         lib = _lib.load()
         if not color.is_cuda:
             raise RuntimeError("eags_raster.losses: tensors must live on a CUDA device (there is no CPU path)")
@@ -48,6 +49,9 @@ class _ImageL1(torch.autograd.Function):
             mask_c = None
             if mask is not None:
                 mask_c = mask.reshape(H, W).to(torch.uint8).contiguous()
+            mask_d = None
+            if mask_depth is not None:
+                mask_d = mask_depth.reshape(H, W).to(torch.uint8).contiguous()
             want_alpha_grad = bool(soft_alpha and alpha is not None and ctx.needs_input_grad[2])
             f32 = dict(dtype=torch.float32, device=dev)
             g_color = torch.empty(3, H, W, **f32)
@@ -55,10 +59,11 @@ class _ImageL1(torch.autograd.Function):
             g_alpha = torch.empty(2, H, W, **f32) if want_alpha_grad else None
             sums = torch.empty(6, **f32)
             scratch = torch.empty(lib.eags_image_l1_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
-            args = _lib.EagsImageL1(W, H, int(bool(soft_alpha)), int(bool(mask_color)), int(norm_mode), float(eps),
+            args = _lib.EagsImageL1(W, H, int(soft_alpha), int(bool(mask_color)), int(norm_mode), float(eps),
                                     color.data_ptr(), depth.data_ptr(),
                                     None if alpha_c is None else alpha_c.data_ptr(), gt_color.data_ptr(),
-                                    gt_depth.data_ptr(), None if mask_c is None else mask_c.data_ptr())
+                                    gt_depth.data_ptr(), None if mask_c is None else mask_c.data_ptr(),
+                                    None if mask_d is None else mask_d.data_ptr(), float(alpha_min))
             stream = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(lib.eags_image_l1_forward(C.byref(args), g_color.data_ptr(), g_depth.data_ptr(),
                                                  None if g_alpha is None else g_alpha.data_ptr(),
@@ -95,7 +100,7 @@ class _ImageL1(torch.autograd.Function):
         if ga is not None:
             d_alpha = ga[0].view(ctx.alpha_shape)
         return (g_color.view(ctx.shapes[0]), g_depth.view(ctx.shapes[1]), d_alpha, None, None, None, None, None,
-                None, None)
+                None, None, None, None)
 
 
 def tracking_losses(color: torch.Tensor, depth: torch.Tensor, alpha: torch.Tensor, gt_color: torch.Tensor,
@@ -112,6 +117,20 @@ def masked_l1_means(color: torch.Tensor, depth: torch.Tensor, gt_color: torch.Te
     """``l1_loss(color[:, mask], gt_color[:, mask]), l1_loss(depth[:, mask], gt_depth[mask])`` of reference
     mapper.py:161-165; plain means when ``mask`` is None."""
     return _ImageL1.apply(color, depth, None, gt_color, gt_depth, mask, False, False, 1, 0.0)
+
+
+def registration_loss(image: torch.Tensor, depth: torch.Tensor, opacity: torch.Tensor, gt_image: torch.Tensor,
+                      gt_depth: torch.Tensor, rgb_mask: Optional[torch.Tensor] = None,
+                      depth_mask: Optional[torch.Tensor] = None, alpha: float = 0.95,
+                      opacity_min: float = 0.95) -> torch.Tensor:
+    """``get_loss_tracking_rgbd`` of the loop-closure registration (reference src/gsr/loss.py:66-95), two kernels:
+    ``alpha * mean(opacity * |image*m - gt*m|) + (1 - alpha) * mean(|depth*dm - gt_depth*dm|)`` with
+    ``m = rgb_mask`` (``gt.sum(0) > rgb_boundary_threshold`` times the camera's grad mask, loss.py:71-75) and
+    ``dm = depth_mask * (opacity > 0.95)`` (``depth_mask = gt_depth > 0.01``, loss.py:88-92).  Masks are
+    (H,W) / (1,H,W) bool or uint8; None = all valid.  Gradients flow to image, depth and opacity."""
+    l_rgb, l_depth = _ImageL1.apply(image, depth, opacity, gt_image, gt_depth, rgb_mask, 2, True, 2, 0.0,
+                                    depth_mask, float(opacity_min))
+    return alpha * l_rgb + (1.0 - alpha) * l_depth
 
 
 class _Ssim(torch.autograd.Function):

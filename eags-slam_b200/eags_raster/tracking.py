@@ -120,3 +120,28 @@ def update_pose_se3(theta: torch.Tensor, rho: torch.Tensor, viewmatrix: torch.Te
                                             projmatrix_raw.data_ptr(), projmatrix.data_ptr(), campos.data_ptr(),
                                             None if tau_norm is None else tau_norm.data_ptr(), stream),
                    "eags_pose_se3_update")
+
+
+class PoseAdamSE3:
+    """The optimiser side of one loop-closure registration iteration as ONE kernel
+    (``eags_pose_adam_se3_update``): ``optimizer.step()`` on the two pose deltas (torch.optim.Adam, lr 3 x base
+    for ``cam_rot_delta``, base for ``cam_trans_delta``; reference src/gsr/solver.py:38-51,83-91) followed by
+    ``update_pose`` (pose_utils.py:76-93) and the camera properties (camera.py:97-111).  Replaces ~15 tiny
+    optimiser kernels per iteration; CUDA-graph friendly (the step count lives on the device)."""
+
+    def __init__(self, device, base_lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+        self.state = torch.zeros(13, dtype=torch.float32, device=device)
+        self.lr_rot, self.lr_trans, self.betas, self.eps = 3.0 * base_lr, base_lr, betas, eps
+
+    def step(self, theta: torch.Tensor, rho: torch.Tensor, viewmatrix, projmatrix_raw, projmatrix, campos,
+             tau_norm=None) -> None:
+        """Uses ``theta.grad`` / ``rho.grad``; the deltas themselves stay zero (as after ``update_pose``)."""
+        lib = _lib.load()
+        dev = self.state.device
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.eags_pose_adam_se3_update(
+                theta.grad.data_ptr(), rho.grad.data_ptr(), self.state.data_ptr(), self.lr_rot, self.lr_trans,
+                self.betas[0], self.betas[1], self.eps, viewmatrix.data_ptr(), projmatrix_raw.data_ptr(),
+                projmatrix.data_ptr(), campos.data_ptr(), None if tau_norm is None else tau_norm.data_ptr(), stream),
+                "eags_pose_adam_se3_update")

@@ -256,9 +256,12 @@ int eags_peer_adam_step(const EagsPeerRoute* route, const EagsPeerAdam* opt, uin
  * eags_image_l1_backward scales them by upstream_grad / normaliser (device scalars, no host sync). */
 typedef struct EagsImageL1 {
     int32_t width, height;
-    int32_t soft_alpha;    /* weight by alpha^3 (tracker.py:118-121)                               */
+    int32_t soft_alpha;    /* 1: weight both losses by alpha^3 (tracker.py:118-121); 2: registration weighting of
+                              src/gsr/loss.py:66-95 -- colour weight alpha x mask, depth weight mask_depth x
+                              (alpha > alpha_min), no power                                              */
     int32_t mask_color;    /* mask the colour loss as well (tracker.py:122-125)                    */
-    int32_t norm_mode;     /* 0: divide by #(element > 0) (tracker.py:127-128); 1: by #masked      */
+    int32_t norm_mode;     /* 0: divide by #(element > 0) (tracker.py:127-128); 1: by #masked;
+                              2: by the element count (a plain .mean(), src/gsr/loss.py:77,95)        */
     float eps;             /* 1e-8 in the tracker, 0 for a plain L1                                */
     const float* color;    /* (3,H,W) */
     const float* depth;    /* (1,H,W) */
@@ -266,6 +269,8 @@ typedef struct EagsImageL1 {
     const float* gt_color; /* (3,H,W) */
     const float* gt_depth; /* (1,H,W) */
     const uint8_t* mask;   /* (H,W) 0/1 or NULL */
+    const uint8_t* mask_depth; /* (H,W) 0/1 or NULL (= mask): separate validity mask of the depth term  */
+    float alpha_min;       /* soft_alpha == 2: opacity threshold of the depth term (0.95, loss.py:89)  */
 } EagsImageL1;
 size_t eags_image_l1_scratch_bytes(int32_t width, int32_t height);
 /* g_color (3,H,W), g_depth (1,H,W), g_alpha (2,H,W) or NULL, sums4 (SIX floats): device, caller-owned */
@@ -314,6 +319,17 @@ int eags_pose_chain(const float* q, const float* t, const float* viewmatrix, con
  * (`tau.norm() < 1e-4`), readable whenever the host chooses to look.  All pointers device fp32. */
 int eags_pose_se3_update(float* theta, float* rho, float* viewmatrix, const float* projmatrix_raw,
                          float* projmatrix_out, float* campos_out, float* tau_norm, void* stream);
+
+/* The optimiser side of one registration iteration in one launch (reference src/gsr/solver.py:83-91:
+ * `optimizer.step()` on cam_rot_delta / cam_trans_delta -- torch.optim.Adam, lr 3 x base for the rotation, base
+ * for the translation, betas (0.9, 0.999), eps 1e-8 -- then `update_pose`).  The deltas are zero when a step
+ * starts (update_pose zeroes them), so the Adam step is the delta itself; `state13` holds the moments of
+ * (theta, rho) and the step count as 13 device floats, zeroed once by the caller.  Camera outputs as
+ * eags_pose_se3_update. */
+int eags_pose_adam_se3_update(const float* grad_theta, const float* grad_rho, float* state13, float lr_rot,
+                              float lr_trans, float beta1, float beta2, float eps, float* viewmatrix,
+                              const float* projmatrix_raw, float* projmatrix_out, float* campos_out,
+                              float* tau_norm, void* stream);
 
 /* ---- Neighbour queries around keyframe seeding -------------------------------
  * eags_knn_mean_dist2 replaces `simple_knn._C.distCUDA2(points)` (un-vendored pip dependency

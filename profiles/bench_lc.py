@@ -34,7 +34,8 @@ from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianR
 from eags_raster import handoff, scene  # noqa: E402
 from eags_raster.graph import GraphedIteration  # noqa: E402
 from eags_raster.sharded import assign_submaps  # noqa: E402
-from eags_raster.tracking import update_pose_se3  # noqa: E402
+from eags_raster.losses import registration_loss  # noqa: E402
+from eags_raster.tracking import PoseAdamSE3, update_pose_se3  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--submaps", type=int, default=16)
@@ -42,6 +43,9 @@ ap.add_argument("--views", type=int, default=4)
 ap.add_argument("--iters", type=int, default=100)
 ap.add_argument("--P", type=int, default=300_000)
 ap.add_argument("--launch", default="graph", choices=["graph", "eager"])
+ap.add_argument("--host-side", default="fused", choices=["fused", "torch"],
+                help="loss + optimiser + camera update: the fused kernels (registration_loss, PoseAdamSE3) or torch ops + "
+                     "torch.optim.Adam + update_pose_se3")
 ap.add_argument("--json", default=None)
 a = ap.parse_args()
 world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
@@ -141,26 +145,35 @@ for sid in mine:
         raster = GaussianRasterizer(raster_settings=s)
         theta = torch.zeros(3, device=dev, requires_grad=True)
         rho = torch.zeros(3, device=dev, requires_grad=True)
-        opt = torch.optim.Adam([{"params": [theta], "lr": 3e-3}, {"params": [rho], "lr": 1e-3}], capturable=True)
+        fused = a.host_side == "fused"
+        opt = PoseAdamSE3(dev, base_lr=1e-3) if fused else \
+            torch.optim.Adam([{"params": [theta], "lr": 3e-3}, {"params": [rho], "lr": 1e-3}], capturable=True)
         tau_norm = torch.zeros(1, device=dev)
-        rgb_mask = (gt_c.sum(dim=0, keepdim=True) > 0.01).float()
-        depth_mask = (gt_d > 0.01).float()
+        rgb_mask_b, depth_mask_b = gt_c.sum(dim=0) > 0.01, gt_d[0] > 0.01
+        rgb_mask, depth_mask = rgb_mask_b[None].float(), depth_mask_b[None].float()
 
         def iteration():
             if theta.grad is not None:
-                opt.zero_grad(set_to_none=False)
+                theta.grad.zero_()
+                rho.grad.zero_()
             m2d = torch.zeros_like(d["means3D"])
             color, radii, depth, opacity, n_touched = raster(
                 means3D=d["means3D"], means2D=m2d, opacities=d["opacities"], shs=d["shs"], scales=d["scales"],
                 rotations=d["rotations"], theta=theta, rho=rho)
             # get_loss_tracking_rgbd (src/gsr/loss.py:66-95), alpha = 0.95
-            l1_rgb = (opacity * (color * rgb_mask - gt_c * rgb_mask).abs()).mean()
-            dm = depth_mask * (opacity > 0.95).float()
-            loss = 0.95 * l1_rgb + 0.05 * (depth * dm - gt_d * dm).abs().mean()
+            if fused:
+                loss = registration_loss(color, depth, opacity, gt_c, gt_d, rgb_mask_b, depth_mask_b)
+            else:
+                l1_rgb = (opacity * (color * rgb_mask - gt_c * rgb_mask).abs()).mean()
+                dm = depth_mask * (opacity > 0.95).float()
+                loss = 0.95 * l1_rgb + 0.05 * (depth * dm - gt_d * dm).abs().mean()
             loss.backward()
-            opt.step()
             with torch.no_grad():
-                update_pose_se3(theta, rho, view, proj_raw, proj, campos, tau_norm)
+                if fused:
+                    opt.step(theta, rho, view, proj_raw, proj, campos, tau_norm)
+                else:
+                    opt.step()
+                    update_pose_se3(theta, rho, view, proj_raw, proj, campos, tau_norm)
             return loss.detach()
 
         for _ in range(2):
@@ -197,7 +210,7 @@ if rank == 0:
     bytes_sm = a.P * (3 + 3 + 3 + 4 + 1) * 4
     res = {"workload": f"c5: {a.submaps} independent submaps x {a.P} Gaussians, 640x480, {a.views} views x {a.iters} "
                        f"variant-B pose iterations each (Adam + SE3 update per iteration)",
-           "n_gpus": world, "launch": a.launch, "value": a.submaps / ms * 1e3, "unit": "submaps/s",
+           "n_gpus": world, "launch": a.launch, "host_side": a.host_side, "value": a.submaps / ms * 1e3, "unit": "submaps/s",
            "iterations_per_s": a.submaps * a.views * a.iters / ms * 1e3, "ms_per_iteration_per_gpu": ms / max(total_it, 1),
            "collective": "none (replicas only)",
            "handoff": {"submap_bytes": bytes_sm,

@@ -134,3 +134,25 @@ def test_masked_l1_means_against_reference_vectors():
     for leaf, key in ((c, "map_dcolor"), (d, "map_ddepth")):
         ref = torch.from_numpy(g[key]).to(DEV)
         assert float((leaf.grad - ref).abs().max()) <= 1e-5 * float(ref.abs().max()), key
+
+
+def test_registration_loss_matches_the_references_get_loss_tracking_rgbd():
+    """eags_raster.losses.registration_loss against golden vectors produced by the reference's own
+    get_loss_tracking_rgbd (src/gsr/loss.py:66-95) and its autograd gradients
+    (tests/golden/make_golden_registration.py)."""
+    import os
+    import numpy as np
+    from eags_raster.losses import registration_loss
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "registration_reference.npz"))
+    dev = torch.device("cuda")
+    for case in range(3):
+        t = {k: torch.from_numpy(g[f"loss{case}_{k}"]).to(dev) for k in
+             ("image", "depth", "opacity", "gt", "gt_depth", "grad_mask", "loss", "g_image", "g_depth", "g_opacity")}
+        image, depth, opacity = (t[k].clone().requires_grad_(True) for k in ("image", "depth", "opacity"))
+        rgb_mask = (t["gt"].sum(dim=0) > 0.01) & (t["grad_mask"][0] > 0)
+        depth_mask = t["gt_depth"] > 0.01
+        loss = registration_loss(image, depth, opacity, t["gt"], t["gt_depth"][None], rgb_mask, depth_mask)
+        loss.backward()
+        assert abs(float(loss) - float(t["loss"])) <= 1e-6 * abs(float(t["loss"]))
+        for got, want in ((image.grad, t["g_image"]), (depth.grad, t["g_depth"]), (opacity.grad, t["g_opacity"])):
+            assert float((got - want).abs().max()) <= 1e-6 * float(want.abs().max()) + 1e-12
