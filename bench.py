@@ -586,7 +586,7 @@ class MappingJob:
     all-reduce of the fused gradient bucket + isotropic loss + torch.optim.Adam (the baseline).
     ``group_world=False`` = a single-rank job on this device with ALL views (the N = 1 point)."""
 
-    def __init__(self, wl, dev, world, rank, collective, group_world=True):
+    def __init__(self, wl, dev, world, rank, collective, group_world=True, storage_order="tile"):
         from eags_raster import scene
         from gaussian_rasterizer import GaussianRasterizationSettings, GaussianRasterizer
         self.dev, self.world, self.rank, self.collective = dev, world, rank, collective
@@ -595,6 +595,20 @@ class MappingJob:
         self.P = sc["means3D"].shape[0]
         cams = scene.keyframe_views(wl, N_VIEWS)
         self.cam = cams[0]
+        self.storage_order = storage_order
+        if storage_order == "tile":
+            # the mapper owns its parameter storage: keep the submap in the tile order of its first keyframe
+            # (eags_raster.reorder; SLAM seeds Gaussians from keyframe pixels, so this is the order they arrive
+            # in anyway -- SURVEY 8(d)'s random order is the adversarial case for tile binning).  No rendered
+            # value changes.
+            from eags_raster import reorder
+            from types import SimpleNamespace
+            c0 = cams[0]
+            perm = reorder.tile_order(sc["means3D"], SimpleNamespace(
+                viewmatrix=c0.viewmatrix, projmatrix=c0.projmatrix, image_height=c0.H, image_width=c0.W,
+                tanfovx=c0.tanfovx, tanfovy=c0.tanfovy))
+            for k in ("means3D", "scales", "rotations", "opacities", "shs"):
+                sc[k] = sc[k][perm].contiguous()
         self.my = list(range(N_VIEWS)) if self.single else [v for v in range(N_VIEWS) if v % world == rank]
         self.rasters, self.gt_host = [], []
         H, W = self.cam.H, self.cam.W
@@ -839,18 +853,18 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
     collective = args.collective
     if collective == "peer" and world > 1:
         try:
-            job = MappingJob(wl, dev, world, rank, "peer")
+            job = MappingJob(wl, dev, world, rank, "peer", storage_order=args.storage_order)
             flag = torch.zeros(1, device=dev)
         except Exception as e:   # no peer access / symmetric memory on this box: say so, use NCCL
             collective = f"nccl (peer exchange unavailable: {type(e).__name__}: {str(e)[:120]})"
             job, flag = None, torch.ones(1, device=dev)
         dist.all_reduce(flag)        # all ranks must take the same path
         if float(flag) > 0:
-            job = MappingJob(wl, dev, world, rank, "nccl")
+            job = MappingJob(wl, dev, world, rank, "nccl", storage_order=args.storage_order)
             if collective == "peer":
                 collective = "nccl (peer exchange unavailable on another rank)"
     else:
-        job = MappingJob(wl, dev, world, rank, "peer" if collective == "peer" else "nccl")
+        job = MappingJob(wl, dev, world, rank, "peer" if collective == "peer" else "nccl", storage_order=args.storage_order)
     fused = job.adam is not None
 
     def barrier():
@@ -900,7 +914,8 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
         # the strong-scaling baseline measured in the SAME job, on this job's GPUs: all 8 views on one GPU,
         # same kernels, same fused step (a single-rank exchange), no cross-rank wait
         del gi
-        solo = MappingJob(wl, dev, world, rank, "peer" if fused else "nccl", group_world=False)
+        solo = MappingJob(wl, dev, world, rank, "peer" if fused else "nccl", group_world=False,
+                          storage_order=args.storage_order)
         n = max(5, min(steps, 20))
         ms1, _, gi1 = time_mapping(solo, n, 3, flush, use_graph, lambda: torch.cuda.synchronize())
         t1 = torch.tensor([ms1], device=dev, dtype=torch.float64)
@@ -925,7 +940,10 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
                         "collective": collective, "exchange_bytes_per_step": 44 * P,
                         "launch": "cuda-graph replay of the step captured from the public API" if (use_graph and gi) else "eager",
                         "l2": "flushed before every timed step (256 MiB write, outside the events)",
-                        "sh": "frozen (SURVEY 8(e): 11 floats / Gaussian)"},
+                        "sh": "frozen (SURVEY 8(e): 11 floats / Gaussian)",
+                        "storage_order": (job.storage_order + (": the submap is kept in the 16x16-tile order of its first keyframe "
+                                          "(eags_raster.reorder.tile_order; same Gaussians, same images)" if job.storage_order == "tile"
+                                          else ": SURVEY 8(d)'s random order"))},
         "e2e": {"value": N_VIEWS * 1e3 / e2e_ms, "unit": "views/s", "h2d_bytes_per_step": h2d_rank * (world if world > 1 else 1),
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": e2e_ms, "h2d_bytes_per_step_per_rank": h2d_rank,
                 "pipeline": "the step's keyframe images (colour + depth of every view a rank renders) cross PCIe from pinned "
@@ -1264,6 +1282,8 @@ def main():
     ap.add_argument("--workload", default="c2", help="the rasterizer fwd+bwd line (N = 1 headline, c2_weak at N > 1)")
     ap.add_argument("--mapping-workload", default="c4", help="shape of the 8-view sharded-mapping line")
     ap.add_argument("--no-mapping", action="store_true", help="N = 1: skip the `mapping` leg")
+    ap.add_argument("--storage-order", default="tile", choices=["tile", "random"],
+                    help="mapping line: keep the submap's Gaussians in tile order of the first keyframe (default) or as generated")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the `c2_weak` leg")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sync-mode", default=None, choices=["optimistic", "exact", "nosync"])

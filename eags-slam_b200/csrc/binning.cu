@@ -566,10 +566,18 @@ __device__ __forceinline__ void sort_pack_tile(u64* s_keys, RadixSmem<THREADS>& 
 #ifndef SORT_MIN_CTAS
 #define SORT_MIN_CTAS 4
 #endif
+#ifndef SORT_LEAN_CTAS
+#define SORT_LEAN_CTAS 6
+#endif
 constexpr int SORT_ITEMS = EAGS_SORT_SMALL_CAP / SORT_THREADS;
 constexpr int BIG_ITEMS = EAGS_SORT_BIG_CAP / 1024;
 
-__global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_CTAS)
+// LEAN (sort mode 2, the default): only the bucket sort lives in this kernel -- without the radix / bitonic
+// fallbacks it needs ~40 registers instead of 60, so 6 instead of 4 CTAs share an SM (the kernel is bound by
+// global-memory latency at 18 % issue utilisation: more tiles in flight is what helps).  A tile whose depths
+// cluster is appended to `big_list` and sorted by sort_pack_big_kernel, which carries all three sorts.
+template <bool LEAN>
+__global__ void __launch_bounds__(SORT_THREADS, LEAN ? SORT_LEAN_CTAS : SORT_MIN_CTAS)
 sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ unsorted,
                        long long capacity, unsigned tile_cap, int use_radix, PackArgs a) {
     __shared__ __align__(16) unsigned long long s_keys[EAGS_SORT_SMALL_CAP];
@@ -581,9 +589,18 @@ sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ uns
     const int n = (int)(rg.y - rg.x);
     if (n <= 0 || n > EAGS_SORT_SMALL_CAP) return;
     // bucketed forward: the tile's keys sit in its fixed-stride bucket, not at the scanned offset
-    sort_pack_tile<SORT_THREADS, SORT_ITEMS>(s_keys, s_radix,
-                                             unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x), n, rg.x,
-                                             tile, use_radix, a);
+    const unsigned long long* src = unsorted + (tile_cap ? (size_t)tile * tile_cap : (size_t)rg.x);
+    if constexpr (LEAN) {
+        unsigned* s_key = reinterpret_cast<unsigned*>(s_keys);
+        unsigned* s_val = s_key + SORT_THREADS * SORT_ITEMS;
+        if (!bucket_sort_tile<SORT_THREADS, SORT_ITEMS>(s_key, s_val, s_radix, src, n)) {
+            if (threadIdx.x == 0) img.big_list[atomicAdd(&img.ctrl->n_big, 1u)] = tile;   // clustered depths
+            return;
+        }
+        pack_sorted<SORT_THREADS>([=](int k) { return make_uint2(s_key[k], s_val[k]); }, n, rg.x, tile, a);
+    } else {
+        sort_pack_tile<SORT_THREADS, SORT_ITEMS>(s_keys, s_radix, src, n, rg.x, tile, use_radix, a);
+    }
 }
 
 __global__ void __launch_bounds__(1024)
@@ -622,7 +639,10 @@ int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned til
     PackArgs a;
     a.splat_rec = geom.splat_rec;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
-    sort_pack_small_kernel<<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
+    if (use_radix >= 2)
+        sort_pack_small_kernel<true><<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
+    else
+        sort_pack_small_kernel<false><<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);
     if (cudaPeekAtLastError() != cudaSuccess) return -1;
     static const size_t big_smem = (size_t)EAGS_SORT_BIG_CAP * sizeof(unsigned long long) + sizeof(RadixSmem<1024>);
     // opt in to > 48 KB of dynamic shared memory (per device; cheap, idempotent)
