@@ -9,6 +9,8 @@
 //                        combined in fixed order by the last CTA to finish.
 //   K10 image_l1_scale : scales the raw gradients by upstream_grad / normaliser (device scalars).
 // HBM-bound streaming: 9 floats + 1 mask byte read, 5 floats written per pixel.
+#include <initializer_list>
+
 #include "kernels.h"
 
 namespace {
@@ -40,43 +42,107 @@ struct LossArgs {
 
 __device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
 
+// the loss terms and raw gradients of ONE pixel (the arithmetic of the header comment, in one place for the
+// scalar and the 4-pixels-per-thread paths)
+struct PixelOut { float g[3], gd, ga_c, ga_d; };
+__device__ __forceinline__ PixelOut pixel_terms(const LossArgs& a, const float col[3], const float gt[3], float dep,
+                                                float gtd, float al, float m, float md, float& s_c, float& n_c,
+                                                float& s_d, float& n_d) {
+    PixelOut o;
+    const float w = a.soft_alpha == 1 ? al * al * al : 1.f;
+    float wc = w * ((a.mask_color || !a.soft_alpha) ? m : 1.f);   // tracker.py:118-125
+    float wd = w * md;
+    if (a.soft_alpha == 2) {   // registration loss, src/gsr/loss.py:66-95
+        wc = al * m;
+        wd = md * (al > a.alpha_min ? 1.f : 0.f);
+    }
+    float lc_sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const float d = col[c] - gt[c];
+        const float l = (fabsf(d) + a.eps) * wc;
+        lc_sum += fabsf(d) + a.eps;
+        s_c += l;
+        n_c += (a.norm_mode == 0) ? (l > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? m : 1.f);
+        o.g[c] = sgn(d) * wc;
+    }
+    const float dd = dep - gtd;
+    const float ld0 = fabsf(dd) + a.eps;
+    const float ld = ld0 * wd;
+    s_d += ld;
+    n_d += (a.norm_mode == 0) ? (ld > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? md : 1.f);
+    o.gd = sgn(dd) * wd;
+    // d(alpha^3)/dalpha = 3 alpha^2, applied to the unweighted loss terms it multiplies; the colour and depth
+    // parts are scaled by different factors later, so they are kept apart: colour part in slot p, depth
+    // part in slot N + p of g_alpha
+    const float d3 = a.soft_alpha == 1 ? 3.f * al * al : 0.f;
+    o.ga_c = a.soft_alpha == 2 ? lc_sum * m : d3 * lc_sum * ((a.mask_color) ? m : 1.f);
+    o.ga_d = a.soft_alpha == 2 ? 0.f : d3 * ld0 * md;   // (alpha > min) has no gradient
+    return o;
+}
+
+// VEC: four pixels per thread and iteration through 16-byte loads / stores (N % 4 == 0, 16-byte aligned
+// planes -- every torch image of the reference's sizes); all loads of an iteration are issued before its
+// stores.  The scalar path handles any other size.
+template <bool VEC>
 __global__ void __launch_bounds__(LOSS_THREADS)
 image_l1_fwd_kernel(LossArgs a) {
     float s_c = 0.f, n_c = 0.f, s_d = 0.f, n_d = 0.f;
-    for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < a.N; p += gridDim.x * LOSS_THREADS) {
-        const float m = a.mask ? (a.mask[p] ? 1.f : 0.f) : 1.f;
-        const float al = a.alpha ? a.alpha[p] : 1.f;
-        const float md = a.mask_depth ? (a.mask_depth[p] ? 1.f : 0.f) : m;
-        const float w = a.soft_alpha == 1 ? al * al * al : 1.f;
-        float wc = w * ((a.mask_color || !a.soft_alpha) ? m : 1.f);   // tracker.py:118-125
-        float wd = w * md;
-        if (a.soft_alpha == 2) {   // registration loss, src/gsr/loss.py:66-95
-            wc = al * m;
-            wd = md * (al > a.alpha_min ? 1.f : 0.f);
-        }
-        float lc_sum = 0.f;
+    if constexpr (VEC) {
+        const int N4 = a.N >> 2;
+        const size_t N = (size_t)a.N;
+        for (int q = blockIdx.x * LOSS_THREADS + threadIdx.x; q < N4; q += gridDim.x * LOSS_THREADS) {
+            float4 c4[3], t4[3];
 #pragma unroll
-        for (int c = 0; c < 3; c++) {
-            const float d = a.color[(size_t)c * a.N + p] - a.gt_color[(size_t)c * a.N + p];
-            const float l = (fabsf(d) + a.eps) * wc;
-            lc_sum += fabsf(d) + a.eps;
-            s_c += l;
-            n_c += (a.norm_mode == 0) ? (l > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? m : 1.f);
-            a.g_color[(size_t)c * a.N + p] = sgn(d) * wc;
+            for (int c = 0; c < 3; c++) {
+                c4[c] = __ldg(reinterpret_cast<const float4*>(a.color + c * N) + q);
+                t4[c] = __ldg(reinterpret_cast<const float4*>(a.gt_color + c * N) + q);
+            }
+            const float4 d4 = __ldg(reinterpret_cast<const float4*>(a.depth) + q);
+            const float4 e4 = __ldg(reinterpret_cast<const float4*>(a.gt_depth) + q);
+            const float4 al4 = a.alpha ? __ldg(reinterpret_cast<const float4*>(a.alpha) + q) : make_float4(1.f, 1.f, 1.f, 1.f);
+            const uchar4 m4 = a.mask ? __ldg(reinterpret_cast<const uchar4*>(a.mask) + q) : make_uchar4(1, 1, 1, 1);
+            const uchar4 k4 = a.mask_depth ? __ldg(reinterpret_cast<const uchar4*>(a.mask_depth) + q) : m4;
+            const float cc[3][4] = {{c4[0].x, c4[0].y, c4[0].z, c4[0].w}, {c4[1].x, c4[1].y, c4[1].z, c4[1].w},
+                                    {c4[2].x, c4[2].y, c4[2].z, c4[2].w}};
+            const float tt[3][4] = {{t4[0].x, t4[0].y, t4[0].z, t4[0].w}, {t4[1].x, t4[1].y, t4[1].z, t4[1].w},
+                                    {t4[2].x, t4[2].y, t4[2].z, t4[2].w}};
+            const float dv[4] = {d4.x, d4.y, d4.z, d4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
+            const float av[4] = {al4.x, al4.y, al4.z, al4.w};
+            const unsigned char mv[4] = {m4.x, m4.y, m4.z, m4.w}, kv[4] = {k4.x, k4.y, k4.z, k4.w};
+            float og[3][4], ogd[4], oac[4], oad[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float col[3] = {cc[0][u], cc[1][u], cc[2][u]}, gt[3] = {tt[0][u], tt[1][u], tt[2][u]};
+                const PixelOut o = pixel_terms(a, col, gt, dv[u], ev[u], av[u], mv[u] ? 1.f : 0.f, kv[u] ? 1.f : 0.f,
+                                               s_c, n_c, s_d, n_d);
+                og[0][u] = o.g[0]; og[1][u] = o.g[1]; og[2][u] = o.g[2];
+                ogd[u] = o.gd; oac[u] = o.ga_c; oad[u] = o.ga_d;
+            }
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                reinterpret_cast<float4*>(a.g_color + c * N)[q] = make_float4(og[c][0], og[c][1], og[c][2], og[c][3]);
+            reinterpret_cast<float4*>(a.g_depth)[q] = make_float4(ogd[0], ogd[1], ogd[2], ogd[3]);
+            if (a.g_alpha) {
+                reinterpret_cast<float4*>(a.g_alpha)[q] = make_float4(oac[0], oac[1], oac[2], oac[3]);
+                reinterpret_cast<float4*>(a.g_alpha + N)[q] = make_float4(oad[0], oad[1], oad[2], oad[3]);
+            }
         }
-        const float dd = a.depth[p] - a.gt_depth[p];
-        const float ld0 = fabsf(dd) + a.eps;
-        const float ld = ld0 * wd;
-        s_d += ld;
-        n_d += (a.norm_mode == 0) ? (ld > 0.f ? 1.f : 0.f) : (a.norm_mode == 1 ? md : 1.f);
-        a.g_depth[p] = sgn(dd) * wd;
-        if (a.g_alpha) {
-            // d(alpha^3)/dalpha = 3 alpha^2, applied to the unweighted loss terms it multiplies; the
-            // colour and depth parts are scaled by different factors later, so they are kept apart
-            // in the two halves of a float2-like pair: colour part here, depth part in slot N + p.
-            const float d3 = a.soft_alpha == 1 ? 3.f * al * al : 0.f;
-            a.g_alpha[p] = a.soft_alpha == 2 ? lc_sum * m : d3 * lc_sum * ((a.mask_color) ? m : 1.f);
-            a.g_alpha[(size_t)a.N + p] = a.soft_alpha == 2 ? 0.f : d3 * ld0 * md;   // (alpha > min) has no gradient
+    } else {
+        for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < a.N; p += gridDim.x * LOSS_THREADS) {
+            const float m = a.mask ? (a.mask[p] ? 1.f : 0.f) : 1.f;
+            const float md = a.mask_depth ? (a.mask_depth[p] ? 1.f : 0.f) : m;
+            const float al = a.alpha ? a.alpha[p] : 1.f;
+            const float col[3] = {a.color[p], a.color[(size_t)a.N + p], a.color[(size_t)2 * a.N + p]};
+            const float gt[3] = {a.gt_color[p], a.gt_color[(size_t)a.N + p], a.gt_color[(size_t)2 * a.N + p]};
+            const PixelOut o = pixel_terms(a, col, gt, a.depth[p], a.gt_depth[p], al, m, md, s_c, n_c, s_d, n_d);
+#pragma unroll
+            for (int c = 0; c < 3; c++) a.g_color[(size_t)c * a.N + p] = o.g[c];
+            a.g_depth[p] = o.gd;
+            if (a.g_alpha) {
+                a.g_alpha[p] = o.ga_c;
+                a.g_alpha[(size_t)a.N + p] = o.ga_d;
+            }
         }
     }
     // block reduction (fixed order inside the block), then a fixed-order pass over the partials
@@ -120,19 +186,47 @@ image_l1_fwd_kernel(LossArgs a) {
 }
 
 // g *= up / normaliser; `sums` = the forward's out[4]; `up` = {dL/dcolour_loss, dL/ddepth_loss} (device)
+template <bool VEC>
 __global__ void __launch_bounds__(LOSS_THREADS)
 image_l1_scale_kernel(int N, const float* __restrict__ sums, const float* __restrict__ up_c,
                       const float* __restrict__ up_d, float* __restrict__ g_color,
                       float* __restrict__ g_depth, float* __restrict__ g_alpha) {
     const float kc = (sums[1] > 0.f) ? __ldg(up_c) / sums[1] : 0.f;
     const float kd = (sums[3] > 0.f) ? __ldg(up_d) / sums[3] : 0.f;
-    for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += gridDim.x * LOSS_THREADS) {
-        g_color[p] *= kc;
-        g_color[(size_t)N + p] *= kc;
-        g_color[(size_t)2 * N + p] *= kc;
-        g_depth[p] *= kd;
-        if (g_alpha) g_alpha[p] = g_alpha[p] * kc + g_alpha[(size_t)N + p] * kd;
+    if constexpr (VEC) {
+        const int N4 = N >> 2;
+        float4* gc = reinterpret_cast<float4*>(g_color);
+        float4* gd = reinterpret_cast<float4*>(g_depth);
+        float4* ga = reinterpret_cast<float4*>(g_alpha);
+        for (int q = blockIdx.x * LOSS_THREADS + threadIdx.x; q < N4; q += gridDim.x * LOSS_THREADS) {
+            float4 c0 = gc[q], c1 = gc[N4 + q], c2 = gc[2 * N4 + q], d = gd[q];
+            float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+            if (g_alpha) { a0 = ga[q]; a1 = ga[N4 + q]; }
+            c0.x *= kc; c0.y *= kc; c0.z *= kc; c0.w *= kc;
+            c1.x *= kc; c1.y *= kc; c1.z *= kc; c1.w *= kc;
+            c2.x *= kc; c2.y *= kc; c2.z *= kc; c2.w *= kc;
+            d.x *= kd; d.y *= kd; d.z *= kd; d.w *= kd;
+            gc[q] = c0; gc[N4 + q] = c1; gc[2 * N4 + q] = c2; gd[q] = d;
+            if (g_alpha)
+                ga[q] = make_float4(a0.x * kc + a1.x * kd, a0.y * kc + a1.y * kd, a0.z * kc + a1.z * kd, a0.w * kc + a1.w * kd);
+        }
+    } else {
+        for (int p = blockIdx.x * LOSS_THREADS + threadIdx.x; p < N; p += gridDim.x * LOSS_THREADS) {
+            g_color[p] *= kc;
+            g_color[(size_t)N + p] *= kc;
+            g_color[(size_t)2 * N + p] *= kc;
+            g_depth[p] *= kd;
+            if (g_alpha) g_alpha[p] = g_alpha[p] * kc + g_alpha[(size_t)N + p] * kd;
+        }
     }
+}
+
+// 16-byte vector path: N divisible by 4 (so every plane offset c * N keeps the alignment) and aligned bases
+bool vec_ok(int N, std::initializer_list<const void*> ptrs) {
+    if (N & 3) return false;
+    for (const void* p : ptrs)
+        if (p && ((uintptr_t)p & 15)) return false;
+    return true;
 }
 
 int loss_grid(int N) {
@@ -163,17 +257,23 @@ int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_m
     a.ticket = (unsigned*)scratch;
     a.partial = (double*)((char*)scratch + 256);
     a.out = out4;
-    int grid = loss_grid(a.N);
-    if (grid > 148 * 8) grid = 148 * 8;
     if (cudaMemsetAsync(scratch, 0, 256, s) != cudaSuccess) return -1;
-    image_l1_fwd_kernel<<<grid, LOSS_THREADS, 0, s>>>(a);
+    const bool vec = vec_ok(a.N, {color, depth, alpha, gt_color, gt_depth, g_color, g_depth, g_alpha}) &&
+                     (!mask || ((uintptr_t)mask & 3) == 0) && (!mask_depth || ((uintptr_t)mask_depth & 3) == 0);
+    int grid = loss_grid(vec ? a.N / 4 : a.N);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (vec) image_l1_fwd_kernel<true><<<grid, LOSS_THREADS, 0, s>>>(a);
+    else image_l1_fwd_kernel<false><<<grid, LOSS_THREADS, 0, s>>>(a);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
 int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
                           float* g_color, float* g_depth, float* g_alpha, cudaStream_t s) {
     const int N = W * H;
-    image_l1_scale_kernel<<<loss_grid(N), LOSS_THREADS, 0, s>>>(N, sums, up_c, up_d, g_color, g_depth, g_alpha);
+    if (vec_ok(N, {g_color, g_depth, g_alpha}))
+        image_l1_scale_kernel<true><<<loss_grid(N / 4), LOSS_THREADS, 0, s>>>(N, sums, up_c, up_d, g_color, g_depth, g_alpha);
+    else
+        image_l1_scale_kernel<false><<<loss_grid(N), LOSS_THREADS, 0, s>>>(N, sums, up_c, up_d, g_color, g_depth, g_alpha);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

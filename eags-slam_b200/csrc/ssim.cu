@@ -24,22 +24,66 @@ constexpr int SS_THREADS = 256;
 
 struct SsimWindow { float g[2 * R + 1]; };
 
-// separable pass over `NQ` staged quantities: horizontal into s_h, then vertical from s_h
-template <int NQ>
-__device__ __forceinline__ void horizontal_pass(const float (*s_in)[HS][HS + 1], float (*s_h)[HS][TS],
-                                                const SsimWindow& w) {
-    for (int o = threadIdx.x; o < HS * TS; o += SS_THREADS) {
-        const int r = o / TS, c = o - r * TS;
-        float acc[NQ];
+// Register-blocked separable window (round 2).  Round 1 computed every output with its own 11 shared-memory
+// loads per quantity: 84 LDS per pixel, LDS-bound at 109 us for 1752x1168x3.  Now a thread slides the window
+// along the filter direction in registers:
+//   horizontal pass: one thread = one halo row x 8 consecutive output columns: 18 loads per input feed
+//                    8 outputs (lanes run over rows: row stride 43 floats -> conflict-free; the results go to
+//                    s_h with row stride 33 -> conflict-free stores);
+//   vertical pass:   one thread = one column x 4 consecutive output rows: 14 loads per quantity feed 4 outputs
+//                    (lanes run over columns).
+// ~5x fewer shared-memory instructions; the kernels end up FMA-bound.
+constexpr int HB = 8;                 // outputs per thread, horizontal pass
+constexpr int VB = 4;                 // outputs per thread, vertical pass
+constexpr int SH_STRIDE = TS + 1;     // row stride of the horizontally filtered tile
+
+// s_h[q][r][c0 + j] = sum_k g[k] * f_q(in[r][c0 + j + k]) for the NQ quantities produced by `emit`
+template <int NIN, int NQ, typename Emit>
+__device__ __forceinline__ void horizontal_pass(const float (*s_in)[HS][HS + 1], float (*s_h)[HS][SH_STRIDE],
+                                                const SsimWindow& w, Emit emit) {
+    for (int o = threadIdx.x; o < HS * (TS / HB); o += SS_THREADS) {
+        const int seg = o / HS, r = o - seg * HS, c0 = seg * HB;
+        float v[NIN][HB + 2 * R];
 #pragma unroll
-        for (int q = 0; q < NQ; q++) acc[q] = 0.f;
+        for (int i = 0; i < NIN; i++)
 #pragma unroll
-        for (int k = 0; k <= 2 * R; k++) {
+            for (int k = 0; k < HB + 2 * R; k++) v[i][k] = s_in[i][r][c0 + k];
 #pragma unroll
-            for (int q = 0; q < NQ; q++) acc[q] = fmaf(w.g[k], s_in[q][r][c + k], acc[q]);
+        for (int jj = 0; jj < HB; jj++) {
+            float acc[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; q++) acc[q] = 0.f;
+#pragma unroll
+            for (int k = 0; k <= 2 * R; k++) {
+                float in[NIN], f[NQ];
+#pragma unroll
+                for (int i = 0; i < NIN; i++) in[i] = v[i][jj + k];
+                emit(in, f);
+#pragma unroll
+                for (int q = 0; q < NQ; q++) acc[q] = fmaf(w.g[k], f[q], acc[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < NQ; q++) s_h[q][r][c0 + jj] = acc[q];
         }
+    }
+}
+
+// m[q][j] = sum_k g[k] * s_h[q][r0 + j + k][c] for the thread's VB rows
+template <int NQ>
+__device__ __forceinline__ void vertical_window(const float (*s_h)[HS][SH_STRIDE], const SsimWindow& w, int r0, int c,
+                                                float m[NQ][VB]) {
 #pragma unroll
-        for (int q = 0; q < NQ; q++) s_h[q][r][c] = acc[q];
+    for (int q = 0; q < NQ; q++) {
+        float v[VB + 2 * R];
+#pragma unroll
+        for (int k = 0; k < VB + 2 * R; k++) v[k] = s_h[q][r0 + k][c];
+#pragma unroll
+        for (int jj = 0; jj < VB; jj++) {
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k <= 2 * R; k++) acc = fmaf(w.g[k], v[jj + k], acc);
+            m[q][jj] = acc;
+        }
     }
 }
 
@@ -48,7 +92,7 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
                 SsimWindow w, float* __restrict__ part_a, float* __restrict__ part_b,
                 float* __restrict__ part_c, double* __restrict__ sum) {
     __shared__ float s_in[2][HS][HS + 1];     // the two images; the three products are formed on the fly
-    __shared__ float s_h[5][HS][TS];
+    __shared__ float s_h[5][HS][SH_STRIDE];
     __shared__ double s_red[SS_THREADS / 32];
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const float* p1 = img1 + (size_t)ch * H * W;
@@ -61,44 +105,36 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
         s_in[0][r][c] = a; s_in[1][r][c] = b;
     }
     __syncthreads();
-    for (int o = threadIdx.x; o < HS * TS; o += SS_THREADS) {
-        const int r = o / TS, c = o - r * TS;
-        float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int k = 0; k <= 2 * R; k++) {
-            const float a = s_in[0][r][c + k], b = s_in[1][r][c + k], g = w.g[k];
-            acc[0] = fmaf(g, a, acc[0]); acc[1] = fmaf(g, b, acc[1]);
-            acc[2] = fmaf(g, a * a, acc[2]); acc[3] = fmaf(g, b * b, acc[3]); acc[4] = fmaf(g, a * b, acc[4]);
-        }
-#pragma unroll
-        for (int q = 0; q < 5; q++) s_h[q][r][c] = acc[q];
-    }
+    horizontal_pass<2, 5>(s_in, s_h, w, [](const float in[2], float f[5]) {
+        f[0] = in[0]; f[1] = in[1]; f[2] = in[0] * in[0]; f[3] = in[1] * in[1]; f[4] = in[0] * in[1];
+    });
     __syncthreads();
     double local = 0.0;
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-    for (int o = threadIdx.x; o < TS * TS; o += SS_THREADS) {
-        const int r = o / TS, c = o - r * TS;
-        const int y = y0 + r, x = x0 + c;
-        float m[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    {
+        static_assert(TS * (TS / VB) == SS_THREADS, "one vertical item per thread");
+        const int c = threadIdx.x % TS, r0 = (threadIdx.x / TS) * VB;
+        float m[5][VB];
+        vertical_window<5>(s_h, w, r0, c, m);
+        const int x = x0 + c;
 #pragma unroll
-        for (int k = 0; k <= 2 * R; k++) {
-#pragma unroll
-            for (int q = 0; q < 5; q++) m[q] = fmaf(w.g[k], s_h[q][r + k][c], m[q]);
-        }
-        if (y < H && x < W) {
-            const float mu1 = m[0], mu2 = m[1];
-            const float mu1mu2 = mu1 * mu2, mu1sq = mu1 * mu1, mu2sq = mu2 * mu2;
-            const float sig1 = m[2] - mu1sq, sig2 = m[3] - mu2sq, sig12 = m[4] - mu1mu2;
-            const float A1 = 2.f * mu1mu2 + C1, A2 = 2.f * sig12 + C2;
-            const float B1 = mu1sq + mu2sq + C1, B2 = sig1 + sig2 + C2;
-            const float inv = 1.f / (B1 * B2);
-            const float S = A1 * A2 * inv;
-            local += (double)S;
-            const size_t pix = (size_t)ch * H * W + (size_t)y * W + x;
-            // partials of S w.r.t. the three moments img1 enters (mu1, s11 = w*x^2, s12 = w*xy)
-            part_a[pix] = 2.f * mu2 * (A2 - A1) * inv - S * 2.f * mu1 * (1.f / B1 - 1.f / B2);
-            part_b[pix] = -S / B2;
-            part_c[pix] = 2.f * A1 * inv;
+        for (int jj = 0; jj < VB; jj++) {
+            const int y = y0 + r0 + jj;
+            if (y < H && x < W) {
+                const float mu1 = m[0][jj], mu2 = m[1][jj];
+                const float mu1mu2 = mu1 * mu2, mu1sq = mu1 * mu1, mu2sq = mu2 * mu2;
+                const float sig1 = m[2][jj] - mu1sq, sig2 = m[3][jj] - mu2sq, sig12 = m[4][jj] - mu1mu2;
+                const float A1 = 2.f * mu1mu2 + C1, A2 = 2.f * sig12 + C2;
+                const float B1 = mu1sq + mu2sq + C1, B2 = sig1 + sig2 + C2;
+                const float inv = 1.f / (B1 * B2);
+                const float S = A1 * A2 * inv;
+                local += (double)S;
+                const size_t pix = (size_t)ch * H * W + (size_t)y * W + x;
+                // partials of S w.r.t. the three moments img1 enters (mu1, s11 = w*x^2, s12 = w*xy)
+                part_a[pix] = 2.f * mu2 * (A2 - A1) * inv - S * 2.f * mu1 * (1.f / B1 - 1.f / B2);
+                part_b[pix] = -S / B2;
+                part_c[pix] = 2.f * A1 * inv;
+            }
         }
     }
 #pragma unroll
@@ -118,7 +154,7 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
                 const float* __restrict__ part_c, const float* __restrict__ upstream, float inv_count,
                 float* __restrict__ grad1) {
     __shared__ float s_in[3][HS][HS + 1];
-    __shared__ float s_h[3][HS][TS];
+    __shared__ float s_h[3][HS][SH_STRIDE];
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const size_t plane = (size_t)ch * H * W;
     for (int o = threadIdx.x; o < HS * HS; o += SS_THREADS) {
@@ -132,21 +168,19 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
         s_in[0][r][c] = a; s_in[1][r][c] = b; s_in[2][r][c] = cc;
     }
     __syncthreads();
-    horizontal_pass<3>(s_in, s_h, w);
+    horizontal_pass<3, 3>(s_in, s_h, w, [](const float in[3], float f[3]) { f[0] = in[0]; f[1] = in[1]; f[2] = in[2]; });
     __syncthreads();
     const float scale = __ldg(upstream) * inv_count;
-    for (int o = threadIdx.x; o < TS * TS; o += SS_THREADS) {
-        const int r = o / TS, c = o - r * TS;
-        const int y = y0 + r, x = x0 + c;
+    const int c = threadIdx.x % TS, r0 = (threadIdx.x / TS) * VB;
+    float m[3][VB];
+    vertical_window<3>(s_h, w, r0, c, m);
+    const int x = x0 + c;
+#pragma unroll
+    for (int jj = 0; jj < VB; jj++) {
+        const int y = y0 + r0 + jj;
         if (y >= H || x >= W) continue;
-        float m[3] = {0.f, 0.f, 0.f};
-#pragma unroll
-        for (int k = 0; k <= 2 * R; k++) {
-#pragma unroll
-            for (int q = 0; q < 3; q++) m[q] = fmaf(w.g[k], s_h[q][r + k][c], m[q]);
-        }
         const size_t pix = plane + (size_t)y * W + x;
-        grad1[pix] = scale * (m[0] + 2.f * img1[pix] * m[1] + img2[pix] * m[2]);
+        grad1[pix] = scale * (m[0][jj] + 2.f * img1[pix] * m[1][jj] + img2[pix] * m[2][jj]);
     }
 }
 
