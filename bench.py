@@ -950,6 +950,9 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
                             "host memory every step, two steps ahead on a copy stream; the loss is read back every step"},
         "gpu_launches": int(round(launches * steps)), "gpu_launches_per_step": launches,
         "exchange_check": chk, "n1_same_job": n1, "clocks": clocks,
+        "scaling_note": ("strong scaling of THIS metric: compare `value` with `n1_same_job.value` (this job, same GPUs) or "
+                         "with `mapping.value` of the --gpus 1 line; the --gpus 1 line's own `value` is the c2 rasterizer "
+                         "fwd+bwd metric (BASELINE.json's headline), a different workload and unit"),
         "kernels_ms_per_step_rank0": {k: round(v, 4) for k, v in spans_ms.items()},
     }
 
