@@ -15,10 +15,12 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="c2")
 ap.add_argument("--iters", type=int, default=3)
 ap.add_argument("--tma", type=int, default=1)
+ap.add_argument("--P", type=int, default=None)
+ap.add_argument("--variant-b", action="store_true")
 a = ap.parse_args()
 _lib.set_option("tma", a.tma)
 dev = torch.device("cuda:0")
-sc, cam, s = bench.make_workload(a.workload, dev, 0)
+sc, cam, s = bench.make_workload(a.workload, dev, 0, P=a.P)
 keys = ("means3D", "scales", "rotations", "opacities")
 d = {k: sc[k].to(dev) for k in keys + ("shs", "gt_color", "gt_depth")}
 r = GaussianRasterizer(raster_settings=s)
