@@ -360,6 +360,7 @@ __device__ __forceinline__ bool radix_sort_tile(unsigned* s_key, unsigned* s_val
             if (r < rounds && p0 + 32 * r < n) {
                 const unsigned d = ((key[r] - kmin) >> shift) & (RADIX_DIGITS - 1);
                 const unsigned pos = sm.base[d] + cw[d] + lrank[r];
+                EAGS_CHECK(pos < (unsigned)n);
                 s_key[pos] = key[r];
                 s_val[pos] = val[r];
             }
@@ -448,7 +449,10 @@ __device__ __forceinline__ bool bucket_sort_tile(unsigned* s_key, unsigned* s_va
     // ---- histogram
 #pragma unroll
     for (int r = 0; r < ITEMS; r++)
-        if (tid + r * THREADS < n) atomicAdd(&cnt[(key[r] - kmin) >> shift], 1u);
+        if (tid + r * THREADS < n) {
+            EAGS_CHECK(((key[r] - kmin) >> shift) < (unsigned)NB);
+            atomicAdd(&cnt[(key[r] - kmin) >> shift], 1u);
+        }
     __syncthreads();
     // ---- exclusive scan: thread t owns buckets [8 t, 8 t + 8)
     uint4 ca = reinterpret_cast<uint4*>(cnt)[2 * tid], cb = reinterpret_cast<uint4*>(cnt)[2 * tid + 1];
@@ -477,6 +481,7 @@ __device__ __forceinline__ bool bucket_sort_tile(unsigned* s_key, unsigned* s_va
     for (int r = 0; r < ITEMS; r++)
         if (tid + r * THREADS < n) {
             const unsigned pos = atomicAdd(&cnt[(key[r] - kmin) >> shift], 1u);
+            EAGS_CHECK(pos < (unsigned)n);
             s_key[pos] = key[r];
             s_val[pos] = val[r];
         }
@@ -498,6 +503,8 @@ __device__ __forceinline__ bool bucket_sort_tile(unsigned* s_key, unsigned* s_va
 }
 
 struct PackArgs {
+    long long capacity;        // (debug checks)
+    int P;
     const float4* splat_rec;   // [3P] per-Gaussian records written by preprocess_fwd
     uint32_t* point_list;
     float4* records;
@@ -519,6 +526,8 @@ __device__ __forceinline__ void pack_sorted(Get get, int n, unsigned start, unsi
         const float4 g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
         const float4 h0 = __ldg(h), h1 = __ldg(h + 1), h2 = __ldg(h + 2);
         const size_t o = (size_t)start + k;
+        EAGS_CHECK(o < (size_t)a.capacity && (!two || o + THREADS < (size_t)a.capacity));
+        EAGS_CHECK(e.y < (unsigned)a.P && f.y < (unsigned)a.P);
         a.point_list[o] = e.y;
         a.records[3 * o + 0] = g0;
         a.records[3 * o + 1] = g1;
@@ -594,7 +603,11 @@ sort_pack_small_kernel(ImagePtrs img, const unsigned long long* __restrict__ uns
         unsigned* s_key = reinterpret_cast<unsigned*>(s_keys);
         unsigned* s_val = s_key + SORT_THREADS * SORT_ITEMS;
         if (!bucket_sort_tile<SORT_THREADS, SORT_ITEMS>(s_key, s_val, s_radix, src, n)) {
-            if (threadIdx.x == 0) img.big_list[atomicAdd(&img.ctrl->n_big, 1u)] = tile;   // clustered depths
+            if (threadIdx.x == 0) {                                     // clustered depths
+                const unsigned pos = atomicAdd(&img.ctrl->n_big, 1u);
+                EAGS_CHECK(pos < (unsigned)img.G);
+                img.big_list[pos] = tile;
+            }
             return;
         }
         pack_sorted<SORT_THREADS>([=](int k) { return make_uint2(s_key[k], s_val[k]); }, n, rg.x, tile, a);
@@ -634,10 +647,10 @@ int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s) {
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
+int launch_sort_pack(GeomPtrs geom, int P, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
                      cudaStream_t s) {
     PackArgs a;
-    a.splat_rec = geom.splat_rec;
+    a.splat_rec = geom.splat_rec; a.capacity = bin.capacity; a.P = P;
     a.point_list = bin.point_list; a.records = bin.records; a.keys = bin.keys;
     if (use_radix >= 2)
         sort_pack_small_kernel<true><<<img.G, SORT_THREADS, 0, s>>>(img, bin.unsorted, bin.capacity, tile_cap, use_radix, a);

@@ -172,6 +172,7 @@ blend_fwd_kernel(FwdArgs a) {
         const int tile = unit / UNITS_PER_TILE, half = unit % UNITS_PER_TILE;
         const uint2 rg = a.ranges[tile];
         const int n = (int)(rg.y - rg.x);
+        EAGS_CHECK(rg.y >= rg.x && (long long)rg.y <= a.capacity);
         int px, py;
         float rx0, ry0;
         warp_region(tile, a.gx, half * WARPS + warp, lane, px, py, rx0, ry0);

@@ -188,7 +188,7 @@ static int forward_render_impl(const EagsView* view, const EagsGaussians* g, con
     if (out->n_touched && g->P > 0)
         CHECK_CUDA(cudaMemsetAsync(out->n_touched, 0, (size_t)g->P * 4, s), "memset(n_touched)");
     if (tile_cap == 0) CHECK_LAUNCH(launch_duplicate(*view, g->P, radii, geom, img, bin, s), "duplicate");
-    CHECK_LAUNCH(launch_sort_pack(geom, img, bin, (unsigned)tile_cap, g_opt_radix.load(), s), "sort_pack");
+    CHECK_LAUNCH(launch_sort_pack(geom, g->P, img, bin, (unsigned)tile_cap, g_opt_radix.load(), s), "sort_pack");
     CHECK_LAUNCH(launch_blend_fwd(*view, img, bin, *out, g_opt_tma.load(), g_opt_stats.load(), (unsigned)tile_cap, s), "blend_fwd");
     return 0;
 }

@@ -2,9 +2,20 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "../../include/eags_raster.h"
 #include "layout.h"
+
+// Debug build (-DEAGS_DEBUG_CHECKS, profiles/build_variant.sh checks -DEAGS_DEBUG_CHECKS): device-side bounds
+// asserts at every computed index of the binning / packing / blending kernels; a violation traps, so the test
+// suite run against that build fails loudly (compute-sanitizer is not available on the GPU pool).  Compiled
+// out of the product build.
+#ifdef EAGS_DEBUG_CHECKS
+#define EAGS_CHECK(cond) do { if (!(cond)) { printf("EAGS_CHECK failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__); __trap(); } } while (0)
+#else
+#define EAGS_CHECK(cond) do { } while (0)
+#endif
 
 struct GeomPtrs {
     float4* splat_rec;   // [3P], see layout.h
@@ -72,7 +83,7 @@ int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs ge
 int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s);
 int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs geom, ImagePtrs img,
                      BinningPtrs bin, cudaStream_t s);
-int launch_sort_pack(GeomPtrs geom, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
+int launch_sort_pack(GeomPtrs geom, int P, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,
                      cudaStream_t s);
 int launch_blend_fwd(const EagsView& v, ImagePtrs img, BinningPtrs bin, const EagsImages& out,
                      int use_tma, int stats, unsigned tile_cap, cudaStream_t s);

@@ -245,7 +245,10 @@ preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
             r_out = sp.r;
             my_tiles = (unsigned)((sp.x1 - sp.x0) * (sp.y1 - sp.y0));
             for (int y = sp.y0; y < sp.y1; y++)
-                for (int x = sp.x0; x < sp.x1; x++) atomicAdd(&s_hist[y * a.gx + x], 1u);
+                for (int x = sp.x0; x < sp.x1; x++) {
+                    EAGS_CHECK(y >= 0 && x >= 0 && y * a.gx + x < G);
+                    atomicAdd(&s_hist[y * a.gx + x], 1u);
+                }
         }
         radii[i] = r_out;
         geom.tiles_touched[i] = my_tiles;
@@ -275,6 +278,7 @@ preprocess_fwd_agg_kernel(PreArgs a, GeomPtrs geom, int32_t* __restrict__ radii,
             for (int y = y0; y < y1; y++)
                 for (int x = x0; x < x1; x++) {
                     const unsigned t = (unsigned)(y * a.gx + x);
+                    EAGS_CHECK(t < (unsigned)G);
                     const unsigned slot = atomicAdd(&s_hist[t], 1u);
                     if (slot < tile_cap) bucket[(size_t)t * tile_cap + slot] = key;
                     else over = true;
