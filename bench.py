@@ -657,14 +657,14 @@ class MappingJob:
         return self.adam.params() if self.adam is not None else {k: v.detach() for k, v in self.leaf.items()}
 
     def _view_loss(self, act, j):
-        from eags_raster.losses import mapping_color_loss, masked_l1_means
+        from eags_raster.losses import mapping_losses
         m2d = torch.zeros_like(act["means3D"], requires_grad=True)
         image, depth, alpha, radii = self.rasters[j](
             means3D=act["means3D"], means2D=m2d, opacities=act["opacities"], shs=self.shs, colors_precomp=None,
             scales=act["scales"], rotations=act["rotations"], cov3D_precomp=None)
         gt_c, gt_d = self.gt[j]
-        _, depth_loss = masked_l1_means(image, depth, gt_c, gt_d)
-        return mapping_color_loss(image, gt_c, None, LAMBDA_DSSIM) + depth_loss
+        color_loss, depth_loss = mapping_losses(image, depth, gt_c, gt_d, None, LAMBDA_DSSIM)   # mapper.py:161-165
+        return color_loss + depth_loss
 
     def step(self):
         """One optimisation step over the 8-view batch; returns this rank's summed view loss (tensor)."""

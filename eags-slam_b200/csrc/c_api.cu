@@ -424,6 +424,46 @@ int eags_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img1, const
     return 0;
 }
 
+int eags_gaussian_activations(int32_t P, const float* raw_scaling, const float* raw_rotation,
+                              const float* raw_opacity, float* scales, float* rotations, float* opacities,
+                              void* stream) {
+    if (P <= 0 || !raw_scaling || !raw_rotation || !raw_opacity || !scales || !rotations || !opacities ||
+        ((uintptr_t)raw_rotation & 15) || ((uintptr_t)rotations & 15))
+        return fail(EAGS_ERR_INVALID, "eags_gaussian_activations: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_activations(P, raw_scaling, raw_rotation, raw_opacity, scales, rotations, opacities, s),
+                 "activations");
+    return 0;
+}
+
+size_t eags_mapping_loss_scratch_bytes(int32_t W, int32_t H) { return mapping_loss_scratch_bytes(W, H); }
+
+static bool mapping_loss_ok(const EagsMappingLoss* in) {
+    return in && in->width > 0 && in->height > 0 && in->image && in->depth && in->gt_image && in->gt_depth &&
+           (long long)in->width * in->height < (1ll << 30);
+}
+
+int eags_mapping_loss_forward(const EagsMappingLoss* in, void* scratch, float* out8, void* stream) {
+    if (!mapping_loss_ok(in) || !scratch || !out8)
+        return fail(EAGS_ERR_INVALID, "eags_mapping_loss_forward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_mapping_loss_fwd(in->width, in->height, in->lambda_dssim, in->image, in->depth, in->gt_image,
+                                         in->gt_depth, in->mask, scratch, out8, s), "mapping_loss_fwd");
+    return 0;
+}
+
+int eags_mapping_loss_backward(const EagsMappingLoss* in, const void* scratch, const float* out8,
+                               const float* up_color, const float* up_depth, float* grad_image,
+                               float* grad_depth, void* stream) {
+    if (!mapping_loss_ok(in) || !scratch || !out8 || !up_color || !up_depth || !grad_image || !grad_depth)
+        return fail(EAGS_ERR_INVALID, "eags_mapping_loss_backward: bad argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CHECK_LAUNCH(launch_mapping_loss_bwd(in->width, in->height, in->lambda_dssim, in->image, in->depth, in->gt_image,
+                                         in->gt_depth, in->mask, scratch, out8, up_color, up_depth, grad_image,
+                                         grad_depth, s), "mapping_loss_bwd");
+    return 0;
+}
+
 int eags_isotropic_loss(int32_t P, const float* scaling, float* raw_grad, void* sum_scratch8, float* out_mean,
                         void* stream) {
     if (P <= 0 || !scaling || !raw_grad || !sum_scratch8 || !out_mean)

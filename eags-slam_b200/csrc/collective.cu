@@ -279,7 +279,32 @@ peer_adam_kernel(EagsPeerRoute r, EagsPeerAdam o, unsigned epoch, float scale, i
     }
 }
 
+// The activations the rasterizer's inputs go through (reference src/entities/gaussian_model.py:103-122:
+// get_scaling = exp, get_rotation = F.normalize, get_opacity = sigmoid), one pass instead of torch's six
+// kernels (exp, norm reduction, clamp, div, sigmoid): per step, not per view, so it only shows once the views
+// are spread over GPUs.  Their chain rule is the one inside peer_adam_kernel above.
+__global__ void __launch_bounds__(256)
+activations_kernel(int P, const float* __restrict__ raw_s, const float* __restrict__ raw_q,
+                   const float* __restrict__ raw_o, float* __restrict__ s, float* __restrict__ q,
+                   float* __restrict__ o) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P) return;
+    const float a = raw_s[3 * (size_t)i], b = raw_s[3 * (size_t)i + 1], c = raw_s[3 * (size_t)i + 2];
+    const float4 r = *reinterpret_cast<const float4*>(raw_q + 4 * (size_t)i);
+    const float op = raw_o[i];
+    s[3 * (size_t)i] = expf(a); s[3 * (size_t)i + 1] = expf(b); s[3 * (size_t)i + 2] = expf(c);
+    const float n = fmaxf(sqrtf(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w), 1e-12f);   // F.normalize eps
+    *reinterpret_cast<float4*>(q + 4 * (size_t)i) = make_float4(r.x / n, r.y / n, r.z / n, r.w / n);
+    o[i] = 1.f / (1.f + expf(-op));
+}
+
 }  // namespace
+
+int launch_activations(int P, const float* raw_s, const float* raw_q, const float* raw_o, float* s, float* q,
+                       float* o, cudaStream_t st) {
+    activations_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, raw_s, raw_q, raw_o, s, q, o);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
 
 size_t peer_flags_bytes() { return eags_align256(sizeof(PeerFlags)); }
 

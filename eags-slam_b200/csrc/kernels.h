@@ -126,10 +126,19 @@ size_t peer_flags_bytes();
 int launch_peer_reduce(const EagsPeerRoute& r, unsigned epoch, float scale, int wait, cudaStream_t s);
 int launch_peer_adam(const EagsPeerRoute& r, const EagsPeerAdam& o, unsigned epoch, float scale, int wait,
                      cudaStream_t s);
+int launch_activations(int P, const float* raw_s, const float* raw_q, const float* raw_o, float* s, float* q,
+                       float* o, cudaStream_t st);
 
 // ssim.cu
 int launch_ssim_fwd(int C, int H, int W, const float* img1, const float* img2, float* part_abc, double* sum,
                     float* out, cudaStream_t s);
 int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, const float* part_abc,
                     const float* upstream, float* grad1, cudaStream_t s);
+size_t mapping_loss_scratch_bytes(int W, int H);
+int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
+                            const float* gt_depth, const uint8_t* mask, void* scratch, float* out8, cudaStream_t s);
+int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
+                            const float* gt_depth, const uint8_t* mask, const void* scratch, const float* out8,
+                            const float* up_color, const float* up_depth, float* grad_image, float* grad_depth,
+                            cudaStream_t s);
 int launch_isotropic(int P, const float* scaling, float* grad, double* sum, float* out, cudaStream_t s);

@@ -13,6 +13,14 @@
 //                     window over the three partial maps; `scale` = upstream gradient / (C H W), read
 //                     from device memory (no host sync).
 // HBM-bound streaming with a 10-pixel halo; no tensor cores (an 11-tap separable stencil).
+//
+// FUSE (the whole per-view mapping loss in two kernels, mapper.py:161-165):
+//   forward : the tile's centre pixels are already in shared memory, so the masked colour L1 and (channel-0
+//             CTAs) the masked depth L1 are summed in the same pass; per-CTA partials, combined in fixed order
+//             by the last CTA, which also forms  (1 - lambda) L1 + lambda (1 - SSIM)  and the depth loss.
+//   backward: dL/dimage = -lambda up_c dSSIM/dimage + (1 - lambda) up_c sign(image - gt) m / n_c  and
+//             dL/ddepth = up_d sign(depth - gt_depth) m / n_d  (the signs are recomputed from the pixels the
+//             kernel reads anyway: no raw-gradient images, no scaling pass, no autograd adds).
 #include "kernels.h"
 
 namespace {
@@ -23,6 +31,29 @@ constexpr int HS = TS + 2 * R;    // halo tile
 constexpr int SS_THREADS = 256;
 
 struct SsimWindow { float g[2 * R + 1]; };
+
+// the L1 terms of the mapping loss riding on the SSIM kernels (FUSE = true)
+struct MapFwd {
+    const float* depth;        // (H,W) rendered
+    const float* gt_depth;     // (H,W)
+    const uint8_t* mask;       // (H,W) or NULL (all valid)
+    double* partial;           // [n_cta][4] = {SSIM sum, colour |d| sum, depth |d| sum, masked pixels}
+    unsigned* ticket;          // zeroed by the launcher
+    float lambda;
+    float* out;                // [8] = {colour sum, n_c, depth sum, n_d, colour L1, depth L1, SSIM, colour loss}
+};
+struct MapBwd {
+    const float* depth;
+    const float* gt_depth;
+    const uint8_t* mask;
+    const float* out;          // the forward's out[8]
+    const float* up_c;         // dL/d(colour loss), device scalar
+    const float* up_d;         // dL/d(depth loss), device scalar
+    float lambda;
+    float* grad_depth;         // (H,W)
+};
+
+__device__ __forceinline__ float sgnf(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
 
 // Register-blocked separable window (round 2).  Round 1 computed every output with its own 11 shared-memory
 // loads per quantity: 84 LDS per pixel, LDS-bound at 109 us for 1752x1168x3.  Now a thread slides the window
@@ -87,13 +118,14 @@ __device__ __forceinline__ void vertical_window(const float (*s_h)[HS][SH_STRIDE
     }
 }
 
+template <bool FUSE>
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
                 SsimWindow w, float* __restrict__ part_a, float* __restrict__ part_b,
-                float* __restrict__ part_c, double* __restrict__ sum) {
+                float* __restrict__ part_c, double* __restrict__ sum, MapFwd mf) {
     __shared__ float s_in[2][HS][HS + 1];     // the two images; the three products are formed on the fly
     __shared__ float s_h[5][HS][SH_STRIDE];
-    __shared__ double s_red[SS_THREADS / 32];
+    __shared__ double s_red[FUSE ? 4 : 1][SS_THREADS / 32];
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const float* p1 = img1 + (size_t)ch * H * W;
     const float* p2 = img2 + (size_t)ch * H * W;
@@ -110,6 +142,7 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
     });
     __syncthreads();
     double local = 0.0;
+    float l1_c = 0.f, l1_d = 0.f, cnt = 0.f;     // FUSE: at most VB pixels per thread, exact in fp32 order
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
     {
         static_assert(TS * (TS / VB) == SS_THREADS, "one vertical item per thread");
@@ -134,25 +167,98 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
                 part_a[pix] = 2.f * mu2 * (A2 - A1) * inv - S * 2.f * mu1 * (1.f / B1 - 1.f / B2);
                 part_b[pix] = -S / B2;
                 part_c[pix] = 2.f * A1 * inv;
+                if constexpr (FUSE) {
+                    const size_t p2d = (size_t)y * W + x;
+                    const float m = mf.mask ? (mf.mask[p2d] ? 1.f : 0.f) : 1.f;
+                    l1_c += fabsf(s_in[0][r0 + jj + R][c + R] - s_in[1][r0 + jj + R][c + R]) * m;
+                    cnt += m;
+                    if (ch == 0) l1_d += fabsf(__ldg(mf.depth + p2d) - __ldg(mf.gt_depth + p2d)) * m;
+                }
             }
         }
     }
+    if constexpr (!FUSE) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
-    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = local;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int k = 0; k < SS_THREADS / 32; k++) t += s_red[k];
-        atomicAdd(sum, t);
+        for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+        if ((threadIdx.x & 31) == 0) s_red[0][threadIdx.x >> 5] = local;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int k = 0; k < SS_THREADS / 32; k++) t += s_red[0][k];
+            atomicAdd(sum, t);
+        }
+    } else {
+        // per-CTA partials in fixed order, combined in fixed order by the last CTA to finish: the loss value
+        // is reproducible run to run (the gradient only depends on the exact counts anyway)
+        // the L1 sums of a warp (<= 128 terms of magnitude <= a few units) stay in fp32, the count is an integer;
+        // fp64 from the warp totals on
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            local += __shfl_xor_sync(0xffffffffu, local, o);
+            l1_c += __shfl_xor_sync(0xffffffffu, l1_c, o);
+            if (ch == 0) l1_d += __shfl_xor_sync(0xffffffffu, l1_d, o);
+        }
+        const unsigned cnt_w = __reduce_add_sync(0xffffffffu, (unsigned)cnt);
+        if ((threadIdx.x & 31) == 0) {
+            const int wi = threadIdx.x >> 5;
+            s_red[0][wi] = local; s_red[1][wi] = (double)l1_c; s_red[2][wi] = (double)l1_d; s_red[3][wi] = (double)cnt_w;
+        }
+        __syncthreads();
+        const unsigned n_cta = gridDim.x * gridDim.y * gridDim.z, per_ch = gridDim.x * gridDim.y;
+        const unsigned me = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (threadIdx.x < 4) {
+            double t = 0.0;
+#pragma unroll
+            for (int k = 0; k < SS_THREADS / 32; k++) t += s_red[threadIdx.x][k];
+            mf.partial[(size_t)me * 4 + threadIdx.x] = t;
+        }
+        __shared__ bool last;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) last = (atomicAdd(mf.ticket, 1u) == n_cta - 1);
+        __syncthreads();
+        if (!last) return;
+        __threadfence();
+        double t[5] = {0.0, 0.0, 0.0, 0.0, 0.0};   // SSIM, colour, depth, masked elements of all channels, of channel 0
+        for (unsigned b = threadIdx.x; b < n_cta; b += SS_THREADS) {
+            const double c = __ldcg(mf.partial + (size_t)b * 4 + 3);
+            t[0] += __ldcg(mf.partial + (size_t)b * 4);
+            t[1] += __ldcg(mf.partial + (size_t)b * 4 + 1);
+            t[2] += __ldcg(mf.partial + (size_t)b * 4 + 2);
+            t[3] += c;
+            if (b < per_ch) t[4] += c;
+        }
+        __shared__ double s_fin[5][SS_THREADS / 32];
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t[k] += __shfl_xor_sync(0xffffffffu, t[k], o);
+            if ((threadIdx.x & 31) == 0) s_fin[k][threadIdx.x >> 5] = t[k];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double f[5];
+#pragma unroll
+            for (int k = 0; k < 5; k++) {
+                f[k] = 0.0;
+                for (int q = 0; q < SS_THREADS / 32; q++) f[k] += s_fin[k][q];
+            }
+            const float sc = (float)f[1], nc = (float)f[3], sd = (float)f[2], nd = (float)f[4];
+            const float ssim = (float)(f[0] * (1.0 / ((double)C * H * W)));
+            const float l1c = sc / nc, l1d = sd / nd;       // 0/0 -> nan, as the reference's mean of nothing
+            mf.out[0] = sc; mf.out[1] = nc; mf.out[2] = sd; mf.out[3] = nd;
+            mf.out[4] = l1c; mf.out[5] = l1d; mf.out[6] = ssim;
+            mf.out[7] = (1.0f - mf.lambda) * l1c + mf.lambda * (1.0f - ssim);   // mapper.py:162-163
+        }
     }
 }
 
+template <bool FUSE>
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
                 SsimWindow w, const float* __restrict__ part_a, const float* __restrict__ part_b,
                 const float* __restrict__ part_c, const float* __restrict__ upstream, float inv_count,
-                float* __restrict__ grad1) {
+                float* __restrict__ grad1, MapBwd mb) {
     __shared__ float s_in[3][HS][HS + 1];
     __shared__ float s_h[3][HS][SH_STRIDE];
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
@@ -170,7 +276,15 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
     __syncthreads();
     horizontal_pass<3, 3>(s_in, s_h, w, [](const float in[3], float f[3]) { f[0] = in[0]; f[1] = in[1]; f[2] = in[2]; });
     __syncthreads();
-    const float scale = __ldg(upstream) * inv_count;
+    float scale, k_c = 0.f, k_d = 0.f;
+    if constexpr (FUSE) {
+        const float up_c = __ldg(mb.up_c), n_c = __ldg(mb.out + 1), n_d = __ldg(mb.out + 3);
+        scale = -mb.lambda * up_c * inv_count;                   // d(lambda (1 - ssim))
+        k_c = n_c > 0.f ? (1.0f - mb.lambda) * up_c / n_c : 0.f;
+        k_d = n_d > 0.f ? __ldg(mb.up_d) / n_d : 0.f;
+    } else {
+        scale = __ldg(upstream) * inv_count;
+    }
     const int c = threadIdx.x % TS, r0 = (threadIdx.x / TS) * VB;
     float m[3][VB];
     vertical_window<3>(s_h, w, r0, c, m);
@@ -180,7 +294,15 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
         const int y = y0 + r0 + jj;
         if (y >= H || x >= W) continue;
         const size_t pix = plane + (size_t)y * W + x;
-        grad1[pix] = scale * (m[0][jj] + 2.f * img1[pix] * m[1][jj] + img2[pix] * m[2][jj]);
+        const float a = img1[pix], b = img2[pix];
+        float g = scale * (m[0][jj] + 2.f * a * m[1][jj] + b * m[2][jj]);
+        if constexpr (FUSE) {
+            const size_t p2d = (size_t)y * W + x;
+            const float mk = mb.mask ? (mb.mask[p2d] ? 1.f : 0.f) : 1.f;
+            g += k_c * sgnf(a - b) * mk;
+            if (ch == 0) mb.grad_depth[p2d] = k_d * sgnf(__ldg(mb.depth + p2d) - __ldg(mb.gt_depth + p2d)) * mk;
+        }
+        grad1[pix] = g;
     }
 }
 
@@ -206,8 +328,8 @@ int launch_ssim_fwd(int C, int H, int W, const float* img1, const float* img2, f
     const size_t n = (size_t)C * H * W;
     if (cudaMemsetAsync(sum, 0, sizeof(double), s) != cudaSuccess) return -1;
     dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, C);
-    ssim_fwd_kernel<<<grid, SS_THREADS, 0, s>>>(C, H, W, img1, img2, make_window(), part_abc, part_abc + n,
-                                                part_abc + 2 * n, sum);
+    ssim_fwd_kernel<false><<<grid, SS_THREADS, 0, s>>>(C, H, W, img1, img2, make_window(), part_abc, part_abc + n,
+                                                       part_abc + 2 * n, sum, MapFwd{});
     ssim_finish_kernel<<<1, 1, 0, s>>>(sum, 1.f / (float)n, out);
     return cudaPeekAtLastError() == cudaSuccess ? 2 : -1;
 }
@@ -216,7 +338,46 @@ int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, c
                     const float* upstream, float* grad1, cudaStream_t s) {
     const size_t n = (size_t)C * H * W;
     dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, C);
-    ssim_bwd_kernel<<<grid, SS_THREADS, 0, s>>>(C, H, W, img1, img2, make_window(), part_abc, part_abc + n,
-                                                part_abc + 2 * n, upstream, 1.f / (float)n, grad1);
+    ssim_bwd_kernel<false><<<grid, SS_THREADS, 0, s>>>(C, H, W, img1, img2, make_window(), part_abc, part_abc + n,
+                                                       part_abc + 2 * n, upstream, 1.f / (float)n, grad1, MapBwd{});
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ---- the fused per-view mapping loss (three-channel image + depth) ------------------------------------
+// scratch: [3 partial maps of 3 H W floats, 256-aligned][256 B: ticket][n_cta x 4 doubles]
+static size_t map_parts_bytes(int H, int W) { return eags_align256((size_t)3 * 3 * H * W * sizeof(float)); }
+static size_t map_n_cta(int H, int W) { return (size_t)((W + TS - 1) / TS) * ((H + TS - 1) / TS) * 3; }
+
+size_t mapping_loss_scratch_bytes(int W, int H) {
+    return map_parts_bytes(H, W) + 256 + map_n_cta(H, W) * 4 * sizeof(double);
+}
+
+int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
+                            const float* gt_depth, const uint8_t* mask, void* scratch, float* out8, cudaStream_t s) {
+    const size_t n = (size_t)3 * H * W;
+    float* part = (float*)scratch;
+    MapFwd mf;
+    mf.depth = depth; mf.gt_depth = gt_depth; mf.mask = mask; mf.lambda = lambda; mf.out = out8;
+    mf.ticket = (unsigned*)((char*)scratch + map_parts_bytes(H, W));
+    mf.partial = (double*)((char*)scratch + map_parts_bytes(H, W) + 256);
+    if (cudaMemsetAsync(mf.ticket, 0, 256, s) != cudaSuccess) return -1;
+    dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, 3);
+    ssim_fwd_kernel<true><<<grid, SS_THREADS, 0, s>>>(3, H, W, image, gt_image, make_window(), part, part + n,
+                                                      part + 2 * n, nullptr, mf);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
+                            const float* gt_depth, const uint8_t* mask, const void* scratch, const float* out8,
+                            const float* up_color, const float* up_depth, float* grad_image, float* grad_depth,
+                            cudaStream_t s) {
+    const size_t n = (size_t)3 * H * W;
+    const float* part = (const float*)scratch;
+    MapBwd mb;
+    mb.depth = depth; mb.gt_depth = gt_depth; mb.mask = mask; mb.out = out8; mb.up_c = up_color; mb.up_d = up_depth;
+    mb.lambda = lambda; mb.grad_depth = grad_depth;
+    dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, 3);
+    ssim_bwd_kernel<true><<<grid, SS_THREADS, 0, s>>>(3, H, W, image, gt_image, make_window(), part, part + n,
+                                                      part + 2 * n, nullptr, 1.f / (float)n, grad_image, mb);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }

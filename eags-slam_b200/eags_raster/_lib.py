@@ -65,6 +65,14 @@ class EagsImageL1(C.Structure):
     ]
 
 
+class EagsMappingLoss(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("lambda_dssim", C.c_float),
+        ("image", C.c_void_p), ("depth", C.c_void_p), ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p),
+        ("mask", C.c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); also the list tests/test_abi.py checks against include/eags_raster.h
 SIGNATURES = {
     "eags_abi_version": (C.c_int, []),
@@ -111,6 +119,10 @@ SIGNATURES = {
                                     C.c_void_p]),
     "eags_ssim_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
+    "eags_gaussian_activations": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
+    "eags_mapping_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "eags_mapping_loss_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "eags_mapping_loss_backward": (C.c_int, [C.c_void_p] * 8),
     "eags_isotropic_loss": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_pose_compose": (C.c_int, [C.c_void_p] * 9),
     "eags_pose_chain": (C.c_int, [C.c_void_p] * 7),

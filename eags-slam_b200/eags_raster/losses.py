@@ -192,6 +192,74 @@ def mapping_color_loss(image: torch.Tensor, gt_image: torch.Tensor, mask: Option
     return (1.0 - lambda_dssim) * l1 + lambda_dssim * (1.0 - ssim(image, gt_image))
 
 
+class _MappingLoss(torch.autograd.Function):
+    """(colour loss, depth loss) of one mapping view; one forward and one backward kernel."""
+
+    @staticmethod
+    def forward(ctx, image, depth, gt_image, gt_depth, mask, lambda_dssim):
+        lib = _lib.load()
+        if not image.is_cuda:
+            raise RuntimeError("eags_raster.losses: tensors must live on a CUDA device (there is no CPU path)")
+        dev = image.device
+        H, W = int(image.shape[-2]), int(image.shape[-1])
+        with torch.cuda.device(dev):
+            image, depth, gt_image, gt_depth = _c(image), _c(depth), _c(gt_image), _c(gt_depth)
+            if image.numel() != 3 * H * W or depth.numel() != H * W or gt_image.numel() != 3 * H * W or \
+                    gt_depth.numel() != H * W:
+                raise ValueError("expected image (3,H,W), depth (1,H,W) and matching ground truth")
+            mask_c = None if mask is None else mask.reshape(H, W).to(torch.uint8).contiguous()
+            out = torch.empty(8, dtype=torch.float32, device=dev)
+            scratch = torch.empty(lib.eags_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
+            args = _lib.EagsMappingLoss(W, H, float(lambda_dssim), image.data_ptr(), depth.data_ptr(),
+                                        gt_image.data_ptr(), gt_depth.data_ptr(),
+                                        None if mask_c is None else mask_c.data_ptr())
+            _lib.check(lib.eags_mapping_loss_forward(C.byref(args), scratch.data_ptr(), out.data_ptr(),
+                                                     torch.cuda.current_stream(dev).cuda_stream),
+                       "eags_mapping_loss_forward")
+        ctx.save_for_backward(image, depth, gt_image, gt_depth, scratch, out,
+                              mask_c if mask_c is not None else torch.empty(0))
+        ctx.cfg = (H, W, float(lambda_dssim))
+        ctx.shapes = (image.shape, depth.shape)
+        return out[7], out[5]
+
+    @staticmethod
+    def backward(ctx, up_color, up_depth):
+        lib = _lib.load()
+        image, depth, gt_image, gt_depth, scratch, out, mask_c = ctx.saved_tensors
+        H, W, lam = ctx.cfg
+        dev = image.device
+        with torch.cuda.device(dev):
+            zero = None
+            if up_color is None or up_depth is None:
+                zero = torch.zeros((), dtype=torch.float32, device=dev)
+            up_color = _c(up_color) if up_color is not None else zero
+            up_depth = _c(up_depth) if up_depth is not None else zero
+            g_image = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+            g_depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+            args = _lib.EagsMappingLoss(W, H, lam, image.data_ptr(), depth.data_ptr(), gt_image.data_ptr(),
+                                        gt_depth.data_ptr(), mask_c.data_ptr() if mask_c.numel() else None)
+            _lib.check(lib.eags_mapping_loss_backward(C.byref(args), scratch.data_ptr(), out.data_ptr(),
+                                                      up_color.data_ptr(), up_depth.data_ptr(), g_image.data_ptr(),
+                                                      g_depth.data_ptr(),
+                                                      torch.cuda.current_stream(dev).cuda_stream),
+                       "eags_mapping_loss_backward")
+        return g_image.view(ctx.shapes[0]), g_depth.view(ctx.shapes[1]), None, None, None, None
+
+
+def mapping_losses(image: torch.Tensor, depth: torch.Tensor, gt_image: torch.Tensor, gt_depth: torch.Tensor,
+                   mask: Optional[torch.Tensor], lambda_dssim: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``(color_loss, depth_loss)`` of one mapping view, reference src/entities/mapper.py:161-165::
+
+        color_loss = (1 - lambda) * l1_loss(image[:, mask], gt[:, mask]) + lambda * (1 - ssim(image, gt))
+        depth_loss = l1_loss(depth[:, mask], gt_depth[mask])
+
+    in ONE forward and ONE backward kernel (the masked L1 terms ride on the SSIM passes; csrc/ssim.cu).
+    ``mask``: (H,W) / (1,H,W) bool or uint8, None = all valid.  Gradients flow to ``image`` and ``depth``.
+    The same values as ``mapping_color_loss`` + ``masked_l1_means`` (which stay for callers that want the
+    pieces), without their raw-gradient images, scaling passes and autograd adds."""
+    return _MappingLoss.apply(image, depth, gt_image, gt_depth, mask, lambda_dssim)
+
+
 class _Isotropic(torch.autograd.Function):
     @staticmethod
     def forward(ctx, scaling):

@@ -179,12 +179,33 @@ class PeerGradExchange:
         return _RouteCtx(self, float(scale), self.rank if rank is None else rank, reduce, accum, local_views,
                          optimizer)
 
-    def _local_sums(self):
-        """(sums, scratch): two flat 11 x stride fp32 buffers for ``route(local_views > 1)``, made on first use."""
+    def _local_sums(self) -> torch.Tensor:
+        """The flat 11 x stride fp32 buffer of ``route(local_views > 1)``: this rank's gradient sums over the
+        views it already rendered this step (made on first use)."""
         if self._sums is None:
-            self._sums = (torch.zeros(self.flat, dtype=torch.float32, device=self.device),
-                          torch.zeros(self.flat, dtype=torch.float32, device=self.device))
+            self._sums = torch.zeros(self.flat, dtype=torch.float32, device=self.device)
+            self._self_routes = None
         return self._sums
+
+    def _self_route(self, first: bool) -> EagsPeerRoute:
+        """A one-rank route whose only "owner slot" is the local sums buffer: a non-final pass of
+        ``route(local_views > 1)`` goes through the same routed ``preprocess_bwd`` and leaves
+        ``sums = new`` (first pass) or ``sums = sums + new`` (accum = the buffer itself: every CTA reads
+        and writes only its own rows) -- no scratch copy and no separate add pass over 44 B per Gaussian."""
+        acc = self._local_sums()
+        if self._self_routes is None:
+            routes = []
+            for with_acc in (False, True):
+                r = EagsPeerRoute()
+                r.rank, r.world, r.P = 0, 1, self.P
+                r.recv[0] = r.reduced[0] = acc.data_ptr()
+                r.flags[0] = self._bases[self.rank if not self.emulated else 0] + self._off_flags   # never touched
+                if with_acc:
+                    for k, t in enumerate(self._carve(acc).values()):
+                        r.accum[k] = t.data_ptr()
+                routes.append(r)
+            self._self_routes = routes
+        return self._self_routes[0 if first else 1]
 
     def _carve(self, flat: torch.Tensor):
         s, P = self.stride, self.P
@@ -283,10 +304,17 @@ class PeerAdam:
         """dict(means3D, scales, rotations, opacities) for the rasterizer (gaussian_model.py:103-122);
         no autograd graph: the chain rule through the activations is part of the fused step."""
         pv = self.params(rank)
-        with torch.no_grad():
-            return {"means3D": pv["xyz"], "scales": torch.exp(pv["scaling"]),
-                    "rotations": torch.nn.functional.normalize(pv["rotation"]),
-                    "opacities": torch.sigmoid(pv["opacity"])}
+        lib, dev = _lib.load(), self.ex.device
+        P = int(pv["xyz"].shape[0])
+        with torch.no_grad(), torch.cuda.device(dev):
+            f32 = dict(dtype=torch.float32, device=dev)
+            s, q, o = torch.empty(P, 3, **f32), torch.empty(P, 4, **f32), torch.empty(P, 1, **f32)
+            # exp / F.normalize / sigmoid in one kernel (eags_gaussian_activations)
+            _lib.check(lib.eags_gaussian_activations(P, pv["scaling"].data_ptr(), pv["rotation"].data_ptr(),
+                                                     pv["opacity"].data_ptr(), s.data_ptr(), q.data_ptr(),
+                                                     o.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
+                       "eags_gaussian_activations")
+        return {"means3D": pv["xyz"], "scales": s, "rotations": q, "opacities": o}
 
     def steps_taken(self, rank: Optional[int] = None) -> int:
         return int(self._state[self.ex.rank if rank is None else rank][2])
@@ -320,20 +348,14 @@ class _RouteCtx:
         self.passes += 1
         return self.passes == self.local_views
 
-    def pass_targets(self):
-        """Where a non-final pass writes its four rows: the sums themselves (first pass) or scratch."""
-        acc, tmp = self.ex._local_sums()
-        return self.ex._carve(acc if self.passes == 1 else tmp)
-
-    def end_pass(self) -> None:
-        if self.passes > 1:
-            acc, tmp = self.ex._local_sums()
-            acc.add_(tmp)
+    def pass_route(self) -> EagsPeerRoute:
+        """The route of a NON-final pass: into the local sums (stored by the first pass, added to after)."""
+        return self.ex._self_route(first=self.passes == 1)
 
     def pass_accum(self):
         if self.accum is not None:
             return self.accum
-        return self.ex._carve(self.ex._local_sums()[0]) if self.local_views > 1 else None
+        return self.ex._carve(self.ex._local_sums()) if self.local_views > 1 else None
 
     def __enter__(self):
         from . import rasterize

@@ -476,10 +476,6 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                 raise ValueError("PeerGradExchange.route(): the exchange was built for another submap "
                                  f"(P {ex.P} on {ex.device}) or the inputs use cov3D_precomp")
             route_final = route.begin_pass()
-            if not route_final:
-                # an earlier view of this rank's share of the step: a plain backward summed locally
-                arena = dict(arena)
-                arena.update(route.pass_targets())
 
         def buf(name, *shape):
             t = arena.get(name)
@@ -490,14 +486,15 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                 return t.view(*shape)
             return torch.empty(*shape, **f32)
 
+        routed = route is not None     # the four routed rows are written through the route, not through `out`
         out = dict(
-            means3D=buf("means3D", P, 3),
+            means3D=None if routed else buf("means3D", P, 3),
             means2D=buf("means2D", P, 3),
-            opacities=buf("opacities", P, 1),
+            opacities=None if routed else buf("opacities", P, 1),
             shs=buf("shs", P, M, 3) if (shs is not None and want_shs) else None,
             colors_precomp=buf("colors_precomp", P, 3) if colors_precomp is not None else None,
-            scales=buf("scales", P, 3) if scales is not None else None,
-            rotations=buf("rotations", P, 4) if rotations is not None else None,
+            scales=None if routed else (buf("scales", P, 3) if scales is not None else None),
+            rotations=None if routed else (buf("rotations", P, 4) if rotations is not None else None),
             cov3D_precomp=buf("cov3D_precomp", P, 6) if cov3D_precomp is not None else None,
             tau=torch.empty(6, **f32) if want_tau else None,
         ) if not pose_only else dict(
@@ -532,16 +529,21 @@ def rasterize_backward(settings, state: RasterState, means3D, opacities, shs, co
                 if route.do_reduce:
                     ex.reduce(route.scale, route.rank)
                 out.update(ex.reduced_views(route.rank))
+        elif route is not None:
+            # an earlier view of this rank's share of the step: summed into the exchange's local buffer by the
+            # same routed preprocess_bwd (a one-rank route onto that buffer).  The four routed inputs get no
+            # gradient from this pass: the rank's last pass of the step returns the sum over all views of all
+            # ranks (and the chain rule above them runs once)
+            _lib.check(lib.eags_backward_routed(C.byref(view), C.byref(g), state.radii.data_ptr(),
+                                                state.geom.data_ptr(), state.image.data_ptr(),
+                                                state.binning.data_ptr(), state.capacity, C.byref(gin),
+                                                C.byref(gout), scratch.data_ptr(), C.byref(route.pass_route()),
+                                                stream), "eags_backward_routed")
         else:
             _lib.check(lib.eags_backward(C.byref(view), C.byref(g), state.radii.data_ptr(),
                                          state.geom.data_ptr(), state.image.data_ptr(),
                                          state.binning.data_ptr(), state.capacity, C.byref(gin),
                                          C.byref(gout), scratch.data_ptr(), stream), "eags_backward")
-            if route is not None:
-                # the four routed inputs get no gradient from this pass: the rank's last pass of the step
-                # returns the sum over all views of all ranks (and the chain rule above them runs once)
-                route.end_pass()
-                out.update(means3D=None, scales=None, rotations=None, opacities=None)
         if _kernel_stats:
             off = int(lib.eags_backward_stats_offset(P))
             st64 = scratch[off:off + 16].view(torch.int64)

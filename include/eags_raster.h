@@ -246,6 +246,14 @@ typedef struct EagsPeerAdam {
 int eags_peer_adam_step(const EagsPeerRoute* route, const EagsPeerAdam* opt, uint32_t epoch, float scale,
                         int32_t wait, void* stream);
 
+/* The three activations between the optimiser's raw parameters and the rasterizer's inputs
+ * (src/entities/gaussian_model.py:103-122: get_scaling = exp, get_rotation = torch.nn.functional.normalize
+ * (eps 1e-12), get_opacity = sigmoid) in one pass; xyz has none.  raw_rotation / rotations must be 16-byte
+ * aligned.  No gradient: the chain rule through them is part of eags_peer_adam_step. */
+int eags_gaussian_activations(int32_t P, const float* raw_scaling, const float* raw_rotation,
+                              const float* raw_opacity, float* scales, float* rotations, float* opacities,
+                              void* stream);
+
 /* ---- Fused image-space losses ---------------------------------------------
  * The per-iteration losses that bracket the rasterizer in the reference: the tracking loss
  * (src/entities/tracker.py:99-128: |x - y| + eps, depth-valid mask, alpha^3 weighting, each sum
@@ -290,6 +298,30 @@ int eags_ssim_forward(int32_t C, int32_t height, int32_t width, const float* img
                       void* scratch, float* out_mean, void* stream);
 int eags_ssim_backward(int32_t C, int32_t height, int32_t width, const float* img1, const float* img2,
                        const void* scratch, const float* upstream, float* grad_img1, void* stream);
+
+/* The whole per-view mapping loss in two kernels (src/entities/mapper.py:161-165):
+ *   colour loss = (1 - lambda) l1_loss(image[:, mask], gt_image[:, mask]) + lambda (1 - ssim(image, gt_image))
+ *   depth  loss = l1_loss(depth[:, mask], gt_depth[mask])
+ * The masked L1 sums ride on the SSIM forward pass, the sign gradients on the SSIM backward pass: no raw
+ * gradient images, no scaling pass, no gradient adds.  out8 (device, 8 floats) = {colour |d| sum, n_colour,
+ * depth |d| sum, n_depth, colour L1, depth L1, SSIM, colour loss}; the reduction order is fixed (same bits
+ * every run).  backward: grad_image (3,H,W) = up_color[0] d(colour loss)/d image, grad_depth (1,H,W) =
+ * up_depth[0] d(depth loss)/d depth; up_* are device scalars (no host sync).  `scratch`
+ * (eags_mapping_loss_scratch_bytes) and out8 must survive until the backward. */
+typedef struct EagsMappingLoss {
+    int32_t width, height;
+    float lambda_dssim;    /* opt.lambda_dssim (0.2) */
+    const float* image;    /* (3,H,W) rendered */
+    const float* depth;    /* (1,H,W) rendered */
+    const float* gt_image; /* (3,H,W) */
+    const float* gt_depth; /* (1,H,W) */
+    const uint8_t* mask;   /* (H,W) 0/1 or NULL (all valid) */
+} EagsMappingLoss;
+size_t eags_mapping_loss_scratch_bytes(int32_t width, int32_t height);
+int eags_mapping_loss_forward(const EagsMappingLoss* in, void* scratch, float* out8, void* stream);
+int eags_mapping_loss_backward(const EagsMappingLoss* in, const void* scratch, const float* out8,
+                               const float* up_color, const float* up_depth, float* grad_image,
+                               float* grad_depth, void* stream);
 
 /* Isotropic regulariser of the mapping loss (src/entities/losses.py:115-126, mapper.py:166):
  * out_mean = mean |s_ij - mean_j s_ij| over scaling (P,3); raw_grad (P,3) = d(sum)/d scaling (the caller

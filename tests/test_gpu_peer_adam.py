@@ -144,3 +144,30 @@ def test_mapping_steps_through_the_rasterizer(world, per_rank, P):
             for r in range(1, world):
                 assert torch.equal(adam.params(r)[n], got), (step, r, n)
     assert all(ex.error_flag(r) == 0 for r in range(world))
+
+
+def test_fused_activations_match_torch():
+    """eags_gaussian_activations (one kernel) against the reference's activations (gaussian_model.py:77-81:
+    torch.exp, torch.nn.functional.normalize, torch.sigmoid), including a zero quaternion (normalize's eps)
+    and saturated opacities.  Tolerance: 2 ulp-ish relative (expf vs torch's exp), exact zeros stay zeros."""
+    from eags_raster.peer import PeerAdam, PeerGradExchange
+    dev = torch.device("cuda")
+    P = 10_007
+    g = torch.Generator().manual_seed(5)
+    raw = {"xyz": torch.randn(P, 3, generator=g), "scaling": torch.randn(P, 3, generator=g) * 2 - 3,
+           "rotation": torch.randn(P, 4, generator=g) * 3, "opacity": torch.randn(P, 1, generator=g) * 6}
+    raw["rotation"][7] = 0.0
+    raw["opacity"][:4, 0] = torch.tensor([-100.0, 100.0, 0.0, -20.0])
+    raw = {k: v.to(dev) for k, v in raw.items()}
+    ex = PeerGradExchange(P, dev, emulate_world=1)
+    adam = PeerAdam(ex, lr=LR, eps=1e-15)
+    adam.load(raw["xyz"], raw["scaling"], raw["rotation"], raw["opacity"])
+    act = adam.activated()
+    assert act["means3D"].data_ptr() == adam.params()["xyz"].data_ptr()      # xyz has no activation: a view
+    want = {"scales": torch.exp(raw["scaling"]), "rotations": F.normalize(raw["rotation"]),
+            "opacities": torch.sigmoid(raw["opacity"])}
+    for k, w in want.items():
+        assert act[k].shape == w.shape and act[k].is_contiguous()
+        assert float(((act[k] - w).abs() - 4e-7 * w.abs()).max()) <= 1e-38, k
+    assert float(act["rotations"][7].abs().max()) == 0.0
+    assert not any(t.requires_grad for t in act.values())
