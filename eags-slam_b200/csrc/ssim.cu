@@ -17,7 +17,7 @@
 // FUSE (the whole per-view mapping loss in two kernels, mapper.py:161-165):
 //   forward : the tile's centre pixels are already in shared memory, so the masked colour L1 and (channel-0
 //             CTAs) the masked depth L1 are summed in the same pass; per-CTA partials, combined in fixed order
-//             by the last CTA, which also forms  (1 - lambda) L1 + lambda (1 - SSIM)  and the depth loss.
+//             by a one-CTA finish kernel, which also forms  (1 - lambda) L1 + lambda (1 - SSIM)  and the depth loss.
 //   backward: dL/dimage = -lambda up_c dSSIM/dimage + (1 - lambda) up_c sign(image - gt) m / n_c  and
 //             dL/ddepth = up_d sign(depth - gt_depth) m / n_d  (the signs are recomputed from the pixels the
 //             kernel reads anyway: no raw-gradient images, no scaling pass, no autograd adds).
@@ -38,7 +38,6 @@ struct MapFwd {
     const float* gt_depth;     // (H,W)
     const uint8_t* mask;       // (H,W) or NULL (all valid)
     double* partial;           // [n_cta][4] = {SSIM sum, colour |d| sum, depth |d| sum, masked pixels}
-    unsigned* ticket;          // zeroed by the launcher
     float lambda;
     float* out;                // [8] = {colour sum, n_c, depth sum, n_d, colour L1, depth L1, SSIM, colour loss}
 };
@@ -188,8 +187,7 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
             atomicAdd(sum, t);
         }
     } else {
-        // per-CTA partials in fixed order, combined in fixed order by the last CTA to finish: the loss value
-        // is reproducible run to run (the gradient only depends on the exact counts anyway)
+        // per-CTA partials in fixed order (the gradient only depends on the exact counts anyway)
         // the L1 sums of a warp (<= 128 terms of magnitude <= a few units) stay in fp32, the count is an integer;
         // fp64 from the warp totals on
 #pragma unroll
@@ -204,47 +202,49 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
             s_red[0][wi] = local; s_red[1][wi] = (double)l1_c; s_red[2][wi] = (double)l1_d; s_red[3][wi] = (double)cnt_w;
         }
         __syncthreads();
-        const unsigned n_cta = gridDim.x * gridDim.y * gridDim.z, per_ch = gridDim.x * gridDim.y;
         const unsigned me = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
         if (threadIdx.x < 4) {
             double t = 0.0;
 #pragma unroll
             for (int k = 0; k < SS_THREADS / 32; k++) t += s_red[threadIdx.x][k];
-            mf.partial[(size_t)me * 4 + threadIdx.x] = t;
+            mf.partial[(size_t)me * 4 + threadIdx.x] = t;     // combined by mapping_loss_finish_kernel
         }
-        __shared__ bool last;
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) last = (atomicAdd(mf.ticket, 1u) == n_cta - 1);
-        __syncthreads();
-        if (!last) return;
-        __threadfence();
-        double t[5] = {0.0, 0.0, 0.0, 0.0, 0.0};   // SSIM, colour, depth, masked elements of all channels, of channel 0
-        for (unsigned b = threadIdx.x; b < n_cta; b += SS_THREADS) {
-            const double c = __ldcg(mf.partial + (size_t)b * 4 + 3);
-            t[0] += __ldcg(mf.partial + (size_t)b * 4);
-            t[1] += __ldcg(mf.partial + (size_t)b * 4 + 1);
-            t[2] += __ldcg(mf.partial + (size_t)b * 4 + 2);
-            t[3] += c;
-            if (b < per_ch) t[4] += c;
-        }
-        __shared__ double s_fin[5][SS_THREADS / 32];
+    }
+}
+
+// One CTA sums the per-CTA partials in a fixed order (thread t takes CTAs t, t + 1024, ...; then a fixed tree):
+// the loss values are reproducible run to run.  A separate launch instead of a last-CTA epilogue: the epilogue
+// needed a __threadfence in every CTA (which exposed the latency of its 12 partial-map stores per thread) and
+// left ~10 dependent rounds of L2 loads running alone at the end of the kernel.
+constexpr int FIN_THREADS = 1024;
+__global__ void __launch_bounds__(FIN_THREADS)
+mapping_loss_finish_kernel(MapFwd mf, unsigned n_cta, unsigned per_ch, double inv_n) {
+    __shared__ double s_fin[5][FIN_THREADS / 32];
+    double t[5] = {0.0, 0.0, 0.0, 0.0, 0.0};   // SSIM, colour, depth, masked elements of all channels, of channel 0
+    for (unsigned b = threadIdx.x; b < n_cta; b += FIN_THREADS) {
+        const double2 lo = __ldcg(reinterpret_cast<const double2*>(mf.partial + (size_t)b * 4));
+        const double2 hi = __ldcg(reinterpret_cast<const double2*>(mf.partial + (size_t)b * 4 + 2));
+        t[0] += lo.x; t[1] += lo.y; t[2] += hi.x; t[3] += hi.y;
+        if (b < per_ch) t[4] += hi.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t[k] += __shfl_xor_sync(0xffffffffu, t[k], o);
+        if ((threadIdx.x & 31) == 0) s_fin[k][threadIdx.x >> 5] = t[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double f[5];
 #pragma unroll
         for (int k = 0; k < 5; k++) {
+            f[k] = s_fin[k][threadIdx.x];
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) t[k] += __shfl_xor_sync(0xffffffffu, t[k], o);
-            if ((threadIdx.x & 31) == 0) s_fin[k][threadIdx.x >> 5] = t[k];
+            for (int o = 16; o > 0; o >>= 1) f[k] += __shfl_xor_sync(0xffffffffu, f[k], o);
         }
-        __syncthreads();
         if (threadIdx.x == 0) {
-            double f[5];
-#pragma unroll
-            for (int k = 0; k < 5; k++) {
-                f[k] = 0.0;
-                for (int q = 0; q < SS_THREADS / 32; q++) f[k] += s_fin[k][q];
-            }
             const float sc = (float)f[1], nc = (float)f[3], sd = (float)f[2], nd = (float)f[4];
-            const float ssim = (float)(f[0] * (1.0 / ((double)C * H * W)));
+            const float ssim = (float)(f[0] * inv_n);
             const float l1c = sc / nc, l1d = sd / nd;       // 0/0 -> nan, as the reference's mean of nothing
             mf.out[0] = sc; mf.out[1] = nc; mf.out[2] = sd; mf.out[3] = nd;
             mf.out[4] = l1c; mf.out[5] = l1d; mf.out[6] = ssim;
@@ -344,12 +344,12 @@ int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, c
 }
 
 // ---- the fused per-view mapping loss (three-channel image + depth) ------------------------------------
-// scratch: [3 partial maps of 3 H W floats, 256-aligned][256 B: ticket][n_cta x 4 doubles]
+// scratch: [3 partial maps of 3 H W floats, 256-aligned][n_cta x 4 doubles]
 static size_t map_parts_bytes(int H, int W) { return eags_align256((size_t)3 * 3 * H * W * sizeof(float)); }
 static size_t map_n_cta(int H, int W) { return (size_t)((W + TS - 1) / TS) * ((H + TS - 1) / TS) * 3; }
 
 size_t mapping_loss_scratch_bytes(int W, int H) {
-    return map_parts_bytes(H, W) + 256 + map_n_cta(H, W) * 4 * sizeof(double);
+    return map_parts_bytes(H, W) + map_n_cta(H, W) * 4 * sizeof(double);
 }
 
 int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
@@ -358,13 +358,13 @@ int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, cons
     float* part = (float*)scratch;
     MapFwd mf;
     mf.depth = depth; mf.gt_depth = gt_depth; mf.mask = mask; mf.lambda = lambda; mf.out = out8;
-    mf.ticket = (unsigned*)((char*)scratch + map_parts_bytes(H, W));
-    mf.partial = (double*)((char*)scratch + map_parts_bytes(H, W) + 256);
-    if (cudaMemsetAsync(mf.ticket, 0, 256, s) != cudaSuccess) return -1;
+    mf.partial = (double*)((char*)scratch + map_parts_bytes(H, W));
     dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, 3);
     ssim_fwd_kernel<true><<<grid, SS_THREADS, 0, s>>>(3, H, W, image, gt_image, make_window(), part, part + n,
                                                       part + 2 * n, nullptr, mf);
-    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+    mapping_loss_finish_kernel<<<1, FIN_THREADS, 0, s>>>(mf, grid.x * grid.y * grid.z, grid.x * grid.y,
+                                                         1.0 / (double)n);
+    return cudaPeekAtLastError() == cudaSuccess ? 2 : -1;
 }
 
 int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
