@@ -438,6 +438,8 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
     copy_streams = [copy_stream] + [torch.cuda.Stream(device=dev) for _ in range(nsplit - 1)]
     bounds = [host_flat.numel() * c // nsplit for c in range(nsplit + 1)]
     copy_times = [] if os.environ.get("EAGS_BENCH_E2E_TRACE") else None
+    # diagnostics only (the reported number never uses them): drop one leg of the pipeline to see what it costs
+    diag_skip = set(filter(None, os.environ.get("EAGS_BENCH_E2E_SKIP", "").split(",")))   # h2d, d2d, d2h
 
     def prefetch(j):
         evs = []
@@ -448,7 +450,8 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
                 if copy_times is not None and c == 0:
                     t_a = torch.cuda.Event(enable_timing=True)
                     t_a.record(cs)
-                ring[j][bounds[c]:bounds[c + 1]].copy_(host_flat[bounds[c]:bounds[c + 1]], non_blocking=True)
+                if "h2d" not in diag_skip:
+                    ring[j][bounds[c]:bounds[c + 1]].copy_(host_flat[bounds[c]:bounds[c + 1]], non_blocking=True)
                 ev = torch.cuda.Event(enable_timing=copy_times is not None and c == 0)
                 ev.record(cs)
                 if copy_times is not None and c == 0:
@@ -470,13 +473,15 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
             for e_ in ev:
                 cur.wait_event(e_)
             if use_graph:     # this step's inputs: ring slot -> the graph's static input block (D2D)
-                static_flat.copy_(ring[i % RING], non_blocking=True)
+                if "d2d" not in diag_skip:
+                    static_flat.copy_(ring[i % RING], non_blocking=True)
                 loss = gi.replay()
             else:
                 loss = step(ring_views[i % RING])
             # the loss crosses to the host every step (4 B D2H into pinned memory); the host consumes it
             # one step later, as a training loop that logs its loss does, so the read never drains the GPU
-            loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
+            if "d2h" not in diag_skip:
+                loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
             done = torch.cuda.Event()
             done.record(cur)
             ring_free[i % RING] = done
@@ -489,7 +494,7 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
         if pending is not None:
             pending[0].synchronize()
             losses_read.append(float(pending[1]))
-        assert len(losses_read) == n and all(v == v for v in losses_read)
+        assert len(losses_read) == n and (diag_skip or all(v == v for v in losses_read))
         if trace:
             print("[e2e trace] ms between consecutive step completions:",
                   " ".join(f"{(b - a) * 1e3:.2f}" for a, b in zip(trace[:40], trace[1:41])), file=sys.stderr, flush=True)

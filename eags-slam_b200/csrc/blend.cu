@@ -81,6 +81,14 @@ __device__ __forceinline__ float fast_exp2(float x) {   // MUFU.EX2, 2 ulp, flus
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// 16-byte shared-memory load from a 32-bit shared address (+ immediate): the survivor lists below hold the
+// records' shared addresses, so a record is read without any address arithmetic
+template <int OFF>
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr), "n"(OFF));
+    return v;
+}
 constexpr float CULL_MARGIN = 0.02f;   // log2 units (1.4 %) >> any fp32 rounding of the pixel test
 
 // A 16x16 tile is eight 8x4 pixel blocks; block s sits at (8 (s & 1), 4 (s >> 1)); lane l -> (l & 7, l >> 3).
@@ -150,6 +158,7 @@ blend_fwd_kernel(FwdArgs a) {
     __shared__ __align__(8) uint64_t s_bar[FWD_STAGES];
     __shared__ int s_touched[VARIANT_B ? FWD_BATCH : 1];
     __shared__ int s_unit;
+    __shared__ uint32_t s_list[WARPS][FWD_BATCH];   // shared addresses of the batch's survivors, in blend order
 
     if (a.ctrl->num_rendered > (unsigned long long)a.capacity) return;
     if (a.tile_cap && a.ctrl->bucket_overflow) return;
@@ -194,8 +203,7 @@ blend_fwd_kernel(FwdArgs a) {
         // outside the image) flips the sign and keeps the magnitude, so the saturation test below
         // (T (1 - alpha) < 1e-4) also holds for finished pixels and no separate predicate is needed.
         float T = inside ? 1.f : -1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, A = 0.f;
-        int lastj = -1;          // last contributor inside the current batch
-        unsigned last = 0;
+        unsigned last = 0;       // 1 + list position of the pixel's last contributor
         int issued = nb;
 
         for (int b = 0; b < nb; b++) {
@@ -213,67 +221,58 @@ blend_fwd_kernel(FwdArgs a) {
             }
             const float4* rec = s_rec[stage];
             if (!__all_sync(FULL, T < 0.f)) {
-                // pass 1: one splat per lane -> bitmask of the splats that can touch this warp's block
-                unsigned mask[FWD_ROUNDS];
+                // pass 1: one splat per lane; the survivors' record addresses are compacted into a per-warp list
+                // (ballot + popc prefix).  Pass 2 then costs one 4-byte broadcast load per survivor instead of
+                // the seven uniform-datapath / integer instructions of walking a bitmask (brev, flo, add, and,
+                // setp, mov, imad): the loop is issue-bound, so they were 1/5 of it.
+                uint32_t* list = s_list[warp];
+                const uint32_t rec_u32 = smem_u32(rec);
+                const unsigned lt = (1u << lane) - 1u;
+                int nsurv = 0;
 #pragma unroll
                 for (int r = 0; r < FWD_ROUNDS; r++) {
                     const int jj = r * 32 + lane;
                     bool keep = false;
                     if (jj < cnt) keep = splat_may_touch(rec[3 * jj], rec[3 * jj + 1], rec[3 * jj + 2].w, rx0, ry0);
-                    mask[r] = __ballot_sync(FULL, keep);
+                    const unsigned bal = __ballot_sync(FULL, keep);
+                    if (keep) list[nsurv + __popc(bal & lt)] = rec_u32 + 48u * (unsigned)jj;
+                    nsurv += __popc(bal);
                 }
-                // pass 2: front-to-back over the survivors (warp-uniform loop, per-lane predicates)
-                lastj = -1;
-#pragma unroll
-                for (int r = 0; r < FWD_ROUNDS; r++) {
-                    unsigned m = mask[r];
-                    while (m) {
-                        const int j = r * 32 + __ffs(m) - 1;
-                        m &= m - 1;
-                        const float4 r0 = rec[3 * j], r1 = rec[3 * j + 1];
-                        const float dx = r0.x - pxf, dy = r0.y - pyf;
-                        const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
-                        const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
-                        if (STATS) st_iters += (lane == 0);
-#ifndef EAGS_FWD_BRANCHY
-                        // branch-free form (if-converted by the compiler: no BSSY / BSYNC pair per splat; measured
-                        // -1 % at c2, -5 % at c4 against the two `continue`s of the #else branch)
-                        const bool hit = !(power2 > 0.f || alpha < 1.0f / 255.0f);
-                        const float test_T = T * (1.f - alpha);
-                        const bool blend = hit && !(test_T < 0.0001f);
-                        if (hit && !blend) T = -fabsf(T);
-                        if (blend) {
-                            if (STATS) st_pairs++;
-                            const float4 r2 = rec[3 * j + 2];
-                            const float w = alpha * T;
-                            C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
-                            D += r0.w * w;
-                            A += w;
-                            if (VARIANT_B) {
-                                if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
-                            }
-                            T = test_T;
-                            lastj = j;
-                        }
-#else
-                        if (power2 > 0.f || alpha < 1.0f / 255.0f) continue;
-                        const float test_T = T * (1.f - alpha);
-                        if (test_T < 0.0001f) { T = -fabsf(T); continue; }
+                __syncwarp();
+                uint32_t last_ad = 0;
+                auto blend_one = [&](const uint32_t ad) {
+                    const float4 r0 = lds128<0>(ad), r1 = lds128<16>(ad);
+                    const float dx = r0.x - pxf, dy = r0.y - pyf;
+                    const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
+                    const float alpha = fminf(0.99f, r1.w * fast_exp2(power2));
+                    if (STATS) st_iters += (lane == 0);
+                    const bool hit = !(power2 > 0.f || alpha < 1.0f / 255.0f);
+                    const float test_T = T * (1.f - alpha);
+                    const bool blend = hit && !(test_T < 0.0001f);
+                    if (hit && !blend) T = -fabsf(T);
+                    if (blend) {
                         if (STATS) st_pairs++;
-                        const float4 r2 = rec[3 * j + 2];
+                        const float4 r2 = lds128<32>(ad);
                         const float w = alpha * T;
                         C0 += r2.x * w; C1 += r2.y * w; C2 += r2.z * w;
                         D += r0.w * w;
                         A += w;
                         if (VARIANT_B) {
-                            if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[j], 1);   // Q10
+                            if (count_touched && test_T > 0.5f) atomicAdd(&s_touched[(ad - rec_u32) / 48u], 1);   // Q10
                         }
                         T = test_T;
-                        lastj = j;
-#endif
+                        last_ad = ad;
                     }
+                };
+                int k = 0;
+                for (const int head = nsurv & 3; k < head; k++) blend_one(list[k]);
+                for (; k < nsurv; k += 4) {
+                    blend_one(list[k]);
+                    blend_one(list[k + 1]);
+                    blend_one(list[k + 2]);
+                    blend_one(list[k + 3]);
                 }
-                if (lastj >= 0) last = (unsigned)(base + lastj + 1);
+                if (last_ad) last = (unsigned)base + (last_ad - rec_u32) / 48u + 1u;
             }
             const int ndone = __syncthreads_count(T < 0.f ? 1 : 0);
             if (VARIANT_B && count_touched) {

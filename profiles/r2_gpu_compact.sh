@@ -1,0 +1,13 @@
+#!/bin/bash
+# compacted survivor lists in the blend kernels (-DEAGS_COMPACT_LIST): parity on the variant build, per-kernel A/B
+set -x
+mkdir -p gpurun_out
+EAGS_RASTER_LIB=$PWD/variants/compact.so timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_parity_fullsize.py tests/test_gpu_bucketed.py tests/test_gpu_golden.py tests/test_gpu_properties.py tests/test_gpu_shims.py tests/test_gpu_tracking.py tests/test_gpu_graph.py -q -m gpu -x 2>&1 | tail -4 > gpurun_out/compact_pytest.txt
+cat gpurun_out/compact_pytest.txt
+rm -f gpurun_out/compact_ab.txt
+for v in intree compact intree compact; do
+  if [ $v = intree ]; then lib=""; else lib=$PWD/variants/$v.so; fi
+  echo "== $v" >> gpurun_out/compact_ab.txt
+  EAGS_RASTER_LIB=$lib timeout 300 python profiles/kernel_ab.py --workloads c2,c3,c4 --opts radix_sort=2 --orders random --reps 15 >> gpurun_out/compact_ab.txt 2>&1
+done
+cat gpurun_out/compact_ab.txt
