@@ -440,6 +440,10 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
     copy_times = [] if os.environ.get("EAGS_BENCH_E2E_TRACE") else None
     # diagnostics only (the reported number never uses them): drop one leg of the pipeline to see what it costs
     diag_skip = set(filter(None, os.environ.get("EAGS_BENCH_E2E_SKIP", "").split(",")))   # h2d, d2d, d2h
+    if "h2d" in diag_skip:          # the ring still holds the real inputs (copied once, outside the loop)
+        for r_ in ring:
+            r_.copy_(host_flat)
+        torch.cuda.synchronize()
 
     def prefetch(j):
         evs = []
@@ -474,7 +478,11 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
                 cur.wait_event(e_)
             if use_graph:     # this step's inputs: ring slot -> the graph's static input block (D2D)
                 if "d2d" not in diag_skip:
-                    static_flat.copy_(ring[i % RING], non_blocking=True)
+                    # an SM copy (elementwise kernel), NOT cudaMemcpyAsync: a D2D memcpy queues on a copy engine
+                    # and can wait behind the 0.31 ms H2D transfer of a later step (EAGS_BENCH_E2E_SKIP legs,
+                    # profiles/r2/e2e_legs.txt: D2D + D2H add 24 us to the replay when no H2D is in flight, the
+                    # full pipeline cost 80 us on a fast-link box)
+                    torch.mul(ring[i % RING], 1.0, out=static_flat)
                 loss = gi.replay()
             else:
                 loss = step(ring_views[i % RING])
@@ -567,7 +575,7 @@ def c2_line(args, world, rank, local, dev, peaks, numa_cpus, steps, warmup, weak
                     "host_block": hostmem_kind,
                     "h2d_copy_alone": {"before": link_before, "after": link_after,
                                        "note": "the step's block copied alone right before / after the e2e leg"},
-                    "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers; every step's loss is copied D2H and consumed by the host one step later"},
+                    "pipeline": "one pinned block -> one H2D copy per step, issued two steps ahead on a copy stream into a static ring of device buffers, copied into the graph's static input block by an SM kernel (a D2D memcpy queues behind the H2D on the copy engine); every step's loss is copied D2H and consumed by the host one step later"},
             # kernels of this repo launched inside the timed region (counted by the C ABI's launch counter:
             # per step x steps; under graph replay each replay launches the captured kernels once)
             "gpu_launches": int(round(launches * steps)), "gpu_launches_per_step": launches, "eager": eager, "host_cpus_local_to_gpu": numa_cpus,
@@ -829,7 +837,7 @@ def mapping_e2e(job, gi, steps, barrier):
                 q.append(prefetch((i + depth) % RING))
             cur = torch.cuda.current_stream()
             cur.wait_event(ev)
-            job.gt_flat.copy_(ring[i % RING], non_blocking=True)
+            torch.mul(ring[i % RING], 1.0, out=job.gt_flat)     # SM copy: a D2D memcpy would queue behind the H2D (c2_line)
             loss = run()
             loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
             done = torch.cuda.Event()

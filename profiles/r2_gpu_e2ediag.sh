@@ -2,10 +2,10 @@
 # where the e2e step's 0.07 ms over the device-timed step goes: drop one leg of the pipeline at a time
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -q -x 2>&1 | tail -4 > gpurun_out/e2ediag_pytest.txt
-cat gpurun_out/e2ediag_pytest.txt
+true
+true
 rm -f gpurun_out/e2ediag.txt
-for skip in none h2d d2d d2h h2d,d2d,d2h none; do
+for skip in none h2d h2d,d2d h2d,d2h h2d,d2d,d2h none; do
   s=$skip; [ $s = none ] && s=""
   EAGS_BENCH_E2E_SKIP=$s timeout 300 python bench.py --no-mapping --no-cpu --steps 200 --warmup 5 2>/dev/null | tail -1 > /tmp/e.json
   python - "$skip" <<'PY' >> gpurun_out/e2ediag.txt
