@@ -241,6 +241,7 @@ blend_fwd_kernel(FwdArgs a) {
                 __syncwarp();
                 uint32_t last_ad = 0;
                 auto blend_one = [&](const uint32_t ad) {
+                    EAGS_CHECK(ad >= rec_u32 && ad < rec_u32 + 48u * (unsigned)cnt && (ad - rec_u32) % 48u == 0);
                     const float4 r0 = lds128<0>(ad), r1 = lds128<16>(ad);
                     const float dx = r0.x - pxf, dy = r0.y - pyf;
                     const float power2 = (r1.x * dx + r1.y * dy) * dx + (r1.z * dy) * dy;
