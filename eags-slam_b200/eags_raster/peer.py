@@ -57,6 +57,7 @@ def owner_chunk(P: int, world: int) -> int:
 class PeerGradExchange:
     def __init__(self, P: int, device, group=None, emulate_world: Optional[int] = None):
         self.P = int(P)
+        self.group = group
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("PeerGradExchange needs a CUDA device (no CPU fallback)")
@@ -315,6 +316,89 @@ class PeerAdam:
                                                      o.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
                        "eags_gaussian_activations")
         return {"means3D": pv["xyz"], "scales": s, "rotations": q, "opacities": o}
+
+    # ---- the optimiser surgery of a growing / shrinking submap (gaussian_model.py:501-584) ----------------
+    def _full_moments(self):
+        """(m, v): the (11, P) first / second moments of ALL Gaussians (rows: xyz 0-2, scaling 3-5, rotation 6-9,
+        opacity 10), assembled from the owners' slices; identical on every rank."""
+        ex = self.ex
+        chunk = owner_chunk(ex.P, ex.world)
+        if ex.emulated:
+            m = torch.cat([self._state[r][0].view(11, chunk) for r in range(ex.world)], dim=1)
+            v = torch.cat([self._state[r][1].view(11, chunk) for r in range(ex.world)], dim=1)
+        elif ex.world == 1:
+            m, v = self._state[ex.rank][0].view(11, chunk), self._state[ex.rank][1].view(11, chunk)
+        else:
+            import torch.distributed as dist
+            m_loc, v_loc, _ = self._state[ex.rank]
+            out = torch.empty(ex.world, 2, 11 * chunk, dtype=torch.float32, device=ex.device)
+            dist.all_gather_into_tensor(out, torch.stack([m_loc, v_loc]), group=ex.group)
+            m = out[:, 0].reshape(ex.world, 11, chunk).permute(1, 0, 2).reshape(11, ex.world * chunk)
+            v = out[:, 1].reshape(ex.world, 11, chunk).permute(1, 0, 2).reshape(11, ex.world * chunk)
+        return m[:, :ex.P], v[:, :ex.P]
+
+    def resized(self, keep: Optional[torch.Tensor] = None, new: Optional[dict] = None) -> "PeerAdam":
+        """A new PeerAdam (on a new exchange of the new size) after the reference's two kinds of optimiser
+        surgery, applied in this order:
+
+        ``keep`` -- bool (P,) mask of the Gaussians that stay: ``prune_points`` / ``_prune_optimizer``
+        (gaussian_model.py:501-533; mapper.py:206-207, 222-223): parameters AND Adam moments of the kept
+        Gaussians are carried over, the step count is kept;
+        ``new`` -- dict(xyz (n,3), scaling (n,3), rotation (n,4), opacity (n,1)) of RAW parameters appended with
+        zero moments: ``densification_postfix`` / ``cat_tensors_to_optimizer`` (gaussian_model.py:535-583).
+
+        Both arguments must be identical on every rank (they are functions of the replicated parameters); every
+        rank calls this collectively (one all-gather of the moments, one symmetric-memory rendezvous).  The
+        ownership ranges move with P, so the moments are re-sliced; learning rates, betas, eps carry over.
+        Not a per-step operation: the reference prunes three times per ``optimize_submap`` and grows once per
+        mapped frame."""
+        ex = self.ex
+        with torch.no_grad():
+            m, v = self._full_moments()
+            pv = ex.param_views(0 if ex.emulated else None)
+            par = {k: pv[k] for k in self.GROUPS}
+            if keep is not None:
+                keep = keep.reshape(-1).to(device=ex.device, dtype=torch.bool)
+                if keep.numel() != ex.P:
+                    raise ValueError(f"resized(keep=...): mask of {keep.numel()} entries for {ex.P} Gaussians")
+                m, v = m[:, keep], v[:, keep]
+                par = {k: t[keep] for k, t in par.items()}
+            if new is not None:
+                n = int(new["xyz"].shape[0])
+                add = {k: new[k].to(device=ex.device, dtype=torch.float32).reshape(n, -1) for k in self.GROUPS}
+                par = {k: torch.cat([par[k], add[k]]) for k in self.GROUPS}
+                z = torch.zeros(11, n, dtype=torch.float32, device=ex.device)
+                m, v = torch.cat([m, z], dim=1), torch.cat([v, z], dim=1)
+            P2 = int(par["xyz"].shape[0])
+            if P2 == 0:
+                raise ValueError("resized(): no Gaussian left")
+            steps = {r: self._state[r][2].clone() for r in self._state}
+            ex2 = PeerGradExchange(P2, ex.device, emulate_world=ex.world) if ex.emulated \
+                else PeerGradExchange(P2, ex.device, group=ex.group)
+            out = PeerAdam(ex2, lr=dict(self.lr), betas=self.betas, eps=self.eps, isotropic_weight=self.isotropic_weight)
+            chunk2 = owner_chunk(P2, ex2.world)
+            for r in out._state:
+                out.load(par["xyz"], par["scaling"], par["rotation"], par["opacity"], rank=r if ex2.emulated else None)
+                g0, g1 = min(P2, r * chunk2), min(P2, (r + 1) * chunk2)
+                out._state[r][0].view(11, chunk2)[:, :g1 - g0].copy_(m[:, g0:g1])
+                out._state[r][1].view(11, chunk2)[:, :g1 - g0].copy_(v[:, g0:g1])
+                out._state[r][2].copy_(steps[r])
+        return out
+
+    def state_dict(self) -> dict:
+        """A COPY of this rank's optimiser state (moments of the Gaussians it owns + step count): the
+        checkpoint of mapper.py:189-195 (``optimizer.state_dict()``), restorable with ``load_state_dict``."""
+        return {"P": self.ex.P, "world": self.ex.world,
+                "state": {r: tuple(t.clone() for t in st) for r, st in self._state.items()}}
+
+    def load_state_dict(self, sd: dict) -> None:
+        if sd["P"] != self.ex.P or sd["world"] != self.ex.world:
+            raise ValueError("load_state_dict: the checkpoint belongs to a submap of another size (taken before a "
+                             "prune / grow)")
+        with torch.no_grad():
+            for r, st in sd["state"].items():
+                for dst, src in zip(self._state[r], st):
+                    dst.copy_(src)
 
     def steps_taken(self, rank: Optional[int] = None) -> int:
         return int(self._state[self.ex.rank if rank is None else rank][2])

@@ -165,6 +165,20 @@ class ShardedMapper:
         if optimizer is not None:
             self.optimizer = optimizer
 
+    def resize(self, keep: Optional[torch.Tensor] = None, new: Optional[dict] = None):
+        """Prune (``keep`` mask) and / or grow (``new`` raw parameters) the submap held by the fused optimiser:
+        the reference's ``prune_points`` (mapper.py:206-207, 222-223) and ``add_points`` (mapper.py:255)
+        with the optimiser state carried over (:meth:`eags_raster.peer.PeerAdam.resized`).  Collective; the
+        exchange and the fused optimiser are replaced (returned as ``(exchange, fused_optimizer)``); a
+        ``loss_fn`` that closed over the old ``fused_optimizer`` must read ``mapper.fused_optimizer`` instead."""
+        if self.fused_optimizer is None:
+            raise ValueError("ShardedMapper.resize: needs fused_optimizer= (torch parameters are resized by the "
+                             "caller, followed by rebuild())")
+        self.exchange.check()
+        self.fused_optimizer = self.fused_optimizer.resized(keep=keep, new=new)
+        self.exchange = self.fused_optimizer.ex
+        return self.exchange, self.fused_optimizer
+
     def step(self, views: Sequence, loss_fn: Callable, reg_fn: Optional[Callable] = None) -> Dict:
         """One optimisation step over ``views`` (all ranks pass the same list).  Returns the local
         loss sum as a *tensor* (no host sync) and the number of views rendered locally."""

@@ -206,8 +206,56 @@ for it in range(3):
         for k in LR:
             pd_[k].copy_(adam.params()[k])
 assert ex3.error_flag() == 0 and adam.steps_taken() == 3
+
+# prune + grow on real ranks (ShardedMapper.resize -> PeerAdam.resized: one all-gather of the moments, a new
+# symmetric-memory exchange): the kept Gaussians keep parameters and Adam moments, the new ones start at zero
+# moments (gaussian_model.py:501-583).  Reference: the same surgery on the torch optimiser of the NCCL mapper.
+gk = torch.Generator().manual_seed(77)
+keep = (torch.rand(P, generator=gk) > 0.3).to(dev)
+n_new = 1234
+new = {"xyz": (torch.rand(n_new, 3, generator=gk) - 0.5).to(dev) * 2.0, "scaling": (torch.randn(n_new, 3, generator=gk) * 0.3 - 3.5).to(dev),
+       "rotation": torch.randn(n_new, 4, generator=gk).to(dev), "opacity": torch.randn(n_new, 1, generator=gk).to(dev)}
+new["xyz"][:, 2] += 3.0
+new_feat = (torch.rand(n_new, feat_c.shape[1], 3, generator=gk) - 0.5).to(dev)
+ex3, adam = mc.resize(keep=keep, new=new)
+feat_c = torch.cat([feat_c.detach()[keep], new_feat]).requires_grad_(True)
+mc.rebuild([feat_c], torch.optim.SGD([feat_c], lr=0.0))
+names_ = ("xyz", "scaling", "rotation", "opacity")
+for group, k in zip(od.param_groups[:4], names_):
+    p_old = group["params"][0]
+    st = od.state.pop(p_old)
+    data = torch.cat([p_old.detach()[keep], new[k]])
+    for key in ("exp_avg", "exp_avg_sq"):
+        st[key] = torch.cat([st[key][keep], torch.zeros_like(new[k])])
+    p_new = torch.nn.Parameter(data.clone())
+    group["params"][0] = p_new
+    od.state[p_new] = st
+    pd_[k] = p_new
+fg = od.param_groups[4]
+od.state.pop(fg["params"][0], None)
+pd_["features"] = torch.nn.Parameter(feat_c.detach().clone())
+fg["params"][0] = pd_["features"]
+md.rebuild(list(pd_.values()), od)
+P2 = int(keep.sum()) + n_new
+assert adam.ex.P == P2 and adam.steps_taken() == 3
+for it in range(2):
+    mc.step(views, fused_loss)
+    md.step(views, make_loss(pd_))
+    torch.cuda.synchronize()
+    for k, lr in LR.items():
+        a_, b_ = adam.params()[k], pd_[k].detach()
+        close = ((a_ - b_).abs() <= 2e-2 * lr + 1e-6 * b_.abs()).float().mean()
+        assert float(close) >= 0.999, ("fused adam after resize", it, k, float(close))
+        c = a_.clone()
+        dist.broadcast(c, src=0)
+        assert torch.equal(c, a_), ("fused adam after resize", it, k, "replicas differ")
+    with torch.no_grad():
+        for k in LR:
+            pd_[k].copy_(adam.params()[k])
+assert ex3.error_flag() == 0 and adam.steps_taken() == 5
 dist.barrier()
 if rank == 0:
+    print(f"prune + grow ok: {P} -> {P2} Gaussians on {world} ranks, optimiser state carried over, 2 more steps vs torch Adam")
     print(f"fused peer Adam ok: 3 steps of {len(views)} views on {world} ranks vs NCCL + torch Adam, replicas bit-identical")
     print(f"sharded mapper ok: {len(views)} views on {world} ranks (2 per rank), peer exchange + NCCL features vs NCCL only")
     print(f"peer exchange ok: world {world}, P {P}, 3 eager steps + 4 graph replays, max rel diff vs NCCL <= 1e-5, replicas bit-identical")

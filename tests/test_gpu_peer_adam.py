@@ -171,3 +171,97 @@ def test_fused_activations_match_torch():
         assert float(((act[k] - w).abs() - 4e-7 * w.abs()).max()) <= 1e-38, k
     assert float(act["rotations"][7].abs().max()) == 0.0
     assert not any(t.requires_grad for t in act.values())
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_prune_and_grow_carry_the_optimiser_state(world):
+    """PeerAdam.resized against the reference's optimiser surgery (gaussian_model.py:501-583: ``_prune_optimizer``
+    keeps exp_avg / exp_avg_sq of the kept rows, ``cat_tensors_to_optimizer`` appends zeros, the step count is
+    kept) on torch.optim.Adam with the same gradients: 2 steps, prune, 2 steps, grow, 2 steps; the ownership
+    ranges move with P, so the moments cross emulated ranks."""
+    from eags_raster.peer import PeerAdam, PeerGradExchange
+    dev = torch.device("cuda")
+    P, eps = 1501, 1e-8
+    g = torch.Generator().manual_seed(11)
+    raw = {"xyz": torch.randn(P, 3, generator=g), "scaling": torch.randn(P, 3, generator=g) - 3,
+           "rotation": torch.randn(P, 4, generator=g), "opacity": torch.randn(P, 1, generator=g)}
+    raw = {k: v.to(dev) for k, v in raw.items()}
+    order = ("xyz", "scaling", "rotation", "opacity")
+    ref = {k: torch.nn.Parameter(v.clone()) for k, v in raw.items()}
+    opt = torch.optim.Adam([{"params": [ref[k]], "lr": LR[k], "name": k} for k in order], lr=0.0, eps=eps)
+    ex = PeerGradExchange(P, dev, emulate_world=world)
+    adam = PeerAdam(ex, lr=LR, eps=eps, isotropic_weight=0.0)
+    for r in range(world):
+        adam.load(raw["xyz"], raw["scaling"], raw["rotation"], raw["opacity"], rank=r)
+
+    def both_step(seed):
+        """The same RAW-parameter gradient on both sides: PeerAdam sees activated-input gradients, so feed it
+        d(raw)/... through the inverse chain: give torch the chain-ruled gradient of what PeerAdam receives."""
+        n = adam.ex.P
+        gg = torch.Generator().manual_seed(seed)
+        gact = {"means3D": torch.randn(n, 3, generator=gg).to(dev), "scales": torch.randn(n, 3, generator=gg).to(dev),
+                "rotations": torch.randn(n, 4, generator=gg).to(dev), "opacities": torch.randn(n, 1, generator=gg).to(dev)}
+        for r in range(world):          # every emulated rank sends gact / world
+            for src in range(world):
+                rv = adam.ex.recv_views(r, src)
+                for k in gact:
+                    rv[k].copy_(gact[k] / world)
+        for r in range(world):
+            adam.step(1.0, rank=r)
+        opt.zero_grad(set_to_none=True)
+        act = {"means3D": ref["xyz"], "scales": torch.exp(ref["scaling"]), "rotations": F.normalize(ref["rotation"]),
+               "opacities": torch.sigmoid(ref["opacity"])}
+        sum((act[k] * gact[k]).sum() for k in gact).backward()
+        opt.step()
+
+    def compare(tag):
+        torch.cuda.synchronize()
+        for n_ in order:
+            got, want = adam.params(0)[n_], ref[n_].detach()
+            assert got.shape == want.shape, (tag, n_)
+            close = (got - want).abs() <= 2e-2 * LR[n_] + 1e-6 * want.abs()
+            assert float(close.float().mean()) >= 0.999, (tag, n_, float(close.float().mean()))
+            for r in range(1, world):
+                assert torch.equal(adam.params(r)[n_], got), (tag, r, n_)
+
+    def torch_surgery(keep=None, new=None):
+        for group in opt.param_groups:
+            p_old = group["params"][0]
+            st = opt.state.pop(p_old)
+            data, ea, es = p_old.detach(), st["exp_avg"], st["exp_avg_sq"]
+            if keep is not None:
+                data, ea, es = data[keep], ea[keep], es[keep]
+            if new is not None:
+                ext = new[group["name"]]
+                data = torch.cat([data, ext]); ea = torch.cat([ea, torch.zeros_like(ext)])
+                es = torch.cat([es, torch.zeros_like(ext)])
+            p_new = torch.nn.Parameter(data.clone())
+            st["exp_avg"], st["exp_avg_sq"] = ea.clone(), es.clone()
+            group["params"][0] = p_new
+            opt.state[p_new] = st
+            ref[group["name"]] = p_new
+
+    both_step(1); both_step(2); compare("before")
+    keep = (torch.rand(P, generator=g) > 0.37).to(dev)
+    ckpt = adam.state_dict()
+    adam = adam.resized(keep=keep)
+    torch_surgery(keep=keep)
+    assert adam.ex.P == int(keep.sum()) and all(adam.steps_taken(r) == 2 for r in range(world))
+    with pytest.raises(ValueError):
+        adam.load_state_dict(ckpt)                      # taken before the prune
+    compare("pruned")
+    both_step(3); both_step(4); compare("after prune")
+    n_new = 333
+    new = {"xyz": torch.randn(n_new, 3, generator=g).to(dev), "scaling": (torch.randn(n_new, 3, generator=g) - 3).to(dev),
+           "rotation": torch.randn(n_new, 4, generator=g).to(dev), "opacity": torch.randn(n_new, 1, generator=g).to(dev)}
+    adam = adam.resized(new=new)
+    torch_surgery(new=new)
+    assert adam.ex.P == int(keep.sum()) + n_new
+    compare("grown")
+    sd = adam.state_dict()
+    both_step(5); both_step(6); compare("after grow")
+    adam.load_state_dict(sd)                            # restores moments + step count of this size
+    assert all(adam.steps_taken(r) == 4 for r in range(world))
+    with pytest.raises(ValueError):
+        adam.resized(keep=torch.zeros(adam.ex.P, dtype=torch.bool, device=dev))
+    assert all(adam.ex.error_flag(r) == 0 for r in range(world))
