@@ -676,7 +676,8 @@ class MappingJob:
             means3D=act["means3D"], means2D=m2d, opacities=act["opacities"], shs=self.shs, colors_precomp=None,
             scales=act["scales"], rotations=act["rotations"], cov3D_precomp=None)
         gt_c, gt_d = self.gt[j]
-        color_loss, depth_loss = mapping_losses(image, depth, gt_c, gt_d, None, LAMBDA_DSSIM)   # mapper.py:161-165
+        # mapper.py:159-165: mask = (gt_depth > 0) & ~isnan(depth), formed inside the loss kernels
+        color_loss, depth_loss = mapping_losses(image, depth, gt_c, gt_d, "valid_depth", LAMBDA_DSSIM)
         return color_loss + depth_loss
 
     def step(self):

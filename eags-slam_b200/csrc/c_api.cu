@@ -448,7 +448,7 @@ int eags_mapping_loss_forward(const EagsMappingLoss* in, void* scratch, float* o
         return fail(EAGS_ERR_INVALID, "eags_mapping_loss_forward: bad argument");
     cudaStream_t s = (cudaStream_t)stream;
     CHECK_LAUNCH(launch_mapping_loss_fwd(in->width, in->height, in->lambda_dssim, in->image, in->depth, in->gt_image,
-                                         in->gt_depth, in->mask, scratch, out8, s), "mapping_loss_fwd");
+                                         in->gt_depth, in->mask, in->valid_depth_mask, scratch, out8, s), "mapping_loss_fwd");
     return 0;
 }
 
@@ -459,8 +459,8 @@ int eags_mapping_loss_backward(const EagsMappingLoss* in, const void* scratch, c
         return fail(EAGS_ERR_INVALID, "eags_mapping_loss_backward: bad argument");
     cudaStream_t s = (cudaStream_t)stream;
     CHECK_LAUNCH(launch_mapping_loss_bwd(in->width, in->height, in->lambda_dssim, in->image, in->depth, in->gt_image,
-                                         in->gt_depth, in->mask, scratch, out8, up_color, up_depth, grad_image,
-                                         grad_depth, s), "mapping_loss_bwd");
+                                         in->gt_depth, in->mask, in->valid_depth_mask, scratch, out8, up_color, up_depth,
+                                         grad_image, grad_depth, s), "mapping_loss_bwd");
     return 0;
 }
 

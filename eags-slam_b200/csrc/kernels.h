@@ -136,9 +136,10 @@ int launch_ssim_bwd(int C, int H, int W, const float* img1, const float* img2, c
                     const float* upstream, float* grad1, cudaStream_t s);
 size_t mapping_loss_scratch_bytes(int W, int H);
 int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
-                            const float* gt_depth, const uint8_t* mask, void* scratch, float* out8, cudaStream_t s);
-int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
-                            const float* gt_depth, const uint8_t* mask, const void* scratch, const float* out8,
-                            const float* up_color, const float* up_depth, float* grad_image, float* grad_depth,
+                            const float* gt_depth, const uint8_t* mask, int valid_depth, void* scratch, float* out8,
                             cudaStream_t s);
+int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
+                            const float* gt_depth, const uint8_t* mask, int valid_depth, const void* scratch,
+                            const float* out8, const float* up_color, const float* up_depth, float* grad_image,
+                            float* grad_depth, cudaStream_t s);
 int launch_isotropic(int P, const float* scaling, float* grad, double* sum, float* out, cudaStream_t s);

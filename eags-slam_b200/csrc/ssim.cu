@@ -37,6 +37,7 @@ struct MapFwd {
     const float* depth;        // (H,W) rendered
     const float* gt_depth;     // (H,W)
     const uint8_t* mask;       // (H,W) or NULL (all valid)
+    int valid_depth;           // AND the mask with (gt_depth > 0) & !isnan(depth)  (mapper.py:159)
     double* partial;           // [n_cta][4] = {SSIM sum, colour |d| sum, depth |d| sum, masked pixels}
     float lambda;
     float* out;                // [8] = {colour sum, n_c, depth sum, n_d, colour L1, depth L1, SSIM, colour loss}
@@ -45,6 +46,7 @@ struct MapBwd {
     const float* depth;
     const float* gt_depth;
     const uint8_t* mask;
+    int valid_depth;
     const float* out;          // the forward's out[8]
     const float* up_c;         // dL/d(colour loss), device scalar
     const float* up_d;         // dL/d(depth loss), device scalar
@@ -168,10 +170,14 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
                 part_c[pix] = 2.f * A1 * inv;
                 if constexpr (FUSE) {
                     const size_t p2d = (size_t)y * W + x;
-                    const float m = mf.mask ? (mf.mask[p2d] ? 1.f : 0.f) : 1.f;
-                    l1_c += fabsf(s_in[0][r0 + jj + R][c + R] - s_in[1][r0 + jj + R][c + R]) * m;
-                    cnt += m;
-                    if (ch == 0) l1_d += fabsf(__ldg(mf.depth + p2d) - __ldg(mf.gt_depth + p2d)) * m;
+                    bool on = mf.mask ? (mf.mask[p2d] != 0) : true;
+                    float dep = 0.f, gtd = 0.f;
+                    if (mf.valid_depth || ch == 0) { dep = __ldg(mf.depth + p2d); gtd = __ldg(mf.gt_depth + p2d); }
+                    if (mf.valid_depth) on = on && gtd > 0.f && !isnan(dep);
+                    // selects, not products: a masked-out pixel may hold nan (that is what the mask is for)
+                    l1_c += on ? fabsf(s_in[0][r0 + jj + R][c + R] - s_in[1][r0 + jj + R][c + R]) : 0.f;
+                    cnt += on ? 1.f : 0.f;
+                    if (ch == 0) l1_d += on ? fabsf(dep - gtd) : 0.f;
                 }
             }
         }
@@ -298,9 +304,12 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
         float g = scale * (m[0][jj] + 2.f * a * m[1][jj] + b * m[2][jj]);
         if constexpr (FUSE) {
             const size_t p2d = (size_t)y * W + x;
-            const float mk = mb.mask ? (mb.mask[p2d] ? 1.f : 0.f) : 1.f;
-            g += k_c * sgnf(a - b) * mk;
-            if (ch == 0) mb.grad_depth[p2d] = k_d * sgnf(__ldg(mb.depth + p2d) - __ldg(mb.gt_depth + p2d)) * mk;
+            bool on = mb.mask ? (mb.mask[p2d] != 0) : true;
+            float dep = 0.f, gtd = 0.f;
+            if (mb.valid_depth || ch == 0) { dep = __ldg(mb.depth + p2d); gtd = __ldg(mb.gt_depth + p2d); }
+            if (mb.valid_depth) on = on && gtd > 0.f && !isnan(dep);
+            g += on ? k_c * sgnf(a - b) : 0.f;
+            if (ch == 0) mb.grad_depth[p2d] = on ? k_d * sgnf(dep - gtd) : 0.f;
         }
         grad1[pix] = g;
     }
@@ -353,11 +362,12 @@ size_t mapping_loss_scratch_bytes(int W, int H) {
 }
 
 int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
-                            const float* gt_depth, const uint8_t* mask, void* scratch, float* out8, cudaStream_t s) {
+                            const float* gt_depth, const uint8_t* mask, int valid_depth, void* scratch, float* out8,
+                            cudaStream_t s) {
     const size_t n = (size_t)3 * H * W;
     float* part = (float*)scratch;
     MapFwd mf;
-    mf.depth = depth; mf.gt_depth = gt_depth; mf.mask = mask; mf.lambda = lambda; mf.out = out8;
+    mf.depth = depth; mf.gt_depth = gt_depth; mf.mask = mask; mf.valid_depth = valid_depth; mf.lambda = lambda; mf.out = out8;
     mf.partial = (double*)((char*)scratch + map_parts_bytes(H, W));
     dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, 3);
     ssim_fwd_kernel<true><<<grid, SS_THREADS, 0, s>>>(3, H, W, image, gt_image, make_window(), part, part + n,
@@ -368,13 +378,13 @@ int launch_mapping_loss_fwd(int W, int H, float lambda, const float* image, cons
 }
 
 int launch_mapping_loss_bwd(int W, int H, float lambda, const float* image, const float* depth, const float* gt_image,
-                            const float* gt_depth, const uint8_t* mask, const void* scratch, const float* out8,
-                            const float* up_color, const float* up_depth, float* grad_image, float* grad_depth,
-                            cudaStream_t s) {
+                            const float* gt_depth, const uint8_t* mask, int valid_depth, const void* scratch,
+                            const float* out8, const float* up_color, const float* up_depth, float* grad_image,
+                            float* grad_depth, cudaStream_t s) {
     const size_t n = (size_t)3 * H * W;
     const float* part = (const float*)scratch;
     MapBwd mb;
-    mb.depth = depth; mb.gt_depth = gt_depth; mb.mask = mask; mb.out = out8; mb.up_c = up_color; mb.up_d = up_depth;
+    mb.depth = depth; mb.gt_depth = gt_depth; mb.mask = mask; mb.valid_depth = valid_depth; mb.out = out8; mb.up_c = up_color; mb.up_d = up_depth;
     mb.lambda = lambda; mb.grad_depth = grad_depth;
     dim3 grid((W + TS - 1) / TS, (H + TS - 1) / TS, 3);
     ssim_bwd_kernel<true><<<grid, SS_THREADS, 0, s>>>(3, H, W, image, gt_image, make_window(), part, part + n,

@@ -69,7 +69,7 @@ class EagsMappingLoss(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32), ("lambda_dssim", C.c_float),
         ("image", C.c_void_p), ("depth", C.c_void_p), ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p),
-        ("mask", C.c_void_p),
+        ("mask", C.c_void_p), ("valid_depth_mask", C.c_int32),
     ]
 
 

@@ -207,18 +207,21 @@ class _MappingLoss(torch.autograd.Function):
             if image.numel() != 3 * H * W or depth.numel() != H * W or gt_image.numel() != 3 * H * W or \
                     gt_depth.numel() != H * W:
                 raise ValueError("expected image (3,H,W), depth (1,H,W) and matching ground truth")
-            mask_c = None if mask is None else mask.reshape(H, W).to(torch.uint8).contiguous()
+            valid_depth = isinstance(mask, str)
+            if valid_depth and mask != "valid_depth":
+                raise ValueError("mapping_losses: mask is a tensor, None or the string 'valid_depth'")
+            mask_c = None if (mask is None or valid_depth) else mask.reshape(H, W).to(torch.uint8).contiguous()
             out = torch.empty(8, dtype=torch.float32, device=dev)
             scratch = torch.empty(lib.eags_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
             args = _lib.EagsMappingLoss(W, H, float(lambda_dssim), image.data_ptr(), depth.data_ptr(),
                                         gt_image.data_ptr(), gt_depth.data_ptr(),
-                                        None if mask_c is None else mask_c.data_ptr())
+                                        None if mask_c is None else mask_c.data_ptr(), int(valid_depth))
             _lib.check(lib.eags_mapping_loss_forward(C.byref(args), scratch.data_ptr(), out.data_ptr(),
                                                      torch.cuda.current_stream(dev).cuda_stream),
                        "eags_mapping_loss_forward")
         ctx.save_for_backward(image, depth, gt_image, gt_depth, scratch, out,
                               mask_c if mask_c is not None else torch.empty(0))
-        ctx.cfg = (H, W, float(lambda_dssim))
+        ctx.cfg = (H, W, float(lambda_dssim), int(valid_depth))
         ctx.shapes = (image.shape, depth.shape)
         return out[7], out[5]
 
@@ -226,7 +229,7 @@ class _MappingLoss(torch.autograd.Function):
     def backward(ctx, up_color, up_depth):
         lib = _lib.load()
         image, depth, gt_image, gt_depth, scratch, out, mask_c = ctx.saved_tensors
-        H, W, lam = ctx.cfg
+        H, W, lam, valid_depth = ctx.cfg
         dev = image.device
         with torch.cuda.device(dev):
             zero = None
@@ -237,7 +240,8 @@ class _MappingLoss(torch.autograd.Function):
             g_image = torch.empty(3, H, W, dtype=torch.float32, device=dev)
             g_depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
             args = _lib.EagsMappingLoss(W, H, lam, image.data_ptr(), depth.data_ptr(), gt_image.data_ptr(),
-                                        gt_depth.data_ptr(), mask_c.data_ptr() if mask_c.numel() else None)
+                                        gt_depth.data_ptr(), mask_c.data_ptr() if mask_c.numel() else None,
+                                        valid_depth)
             _lib.check(lib.eags_mapping_loss_backward(C.byref(args), scratch.data_ptr(), out.data_ptr(),
                                                       up_color.data_ptr(), up_depth.data_ptr(), g_image.data_ptr(),
                                                       g_depth.data_ptr(),
@@ -254,7 +258,9 @@ def mapping_losses(image: torch.Tensor, depth: torch.Tensor, gt_image: torch.Ten
         depth_loss = l1_loss(depth[:, mask], gt_depth[mask])
 
     in ONE forward and ONE backward kernel (the masked L1 terms ride on the SSIM passes; csrc/ssim.cu).
-    ``mask``: (H,W) / (1,H,W) bool or uint8, None = all valid.  Gradients flow to ``image`` and ``depth``.
+    ``mask``: (H,W) / (1,H,W) bool or uint8, None = all valid, or the string ``"valid_depth"``: the mapper's own
+    mask ``(gt_depth > 0) & ~isnan(depth)`` (mapper.py:159) formed per pixel inside the kernels, without the
+    three torch kernels and the uint8 copy a mask tensor costs per view.  Gradients flow to ``image`` and ``depth``.
     The same values as ``mapping_color_loss`` + ``masked_l1_means`` (which stay for callers that want the
     pieces), without their raw-gradient images, scaling passes and autograd adds."""
     return _MappingLoss.apply(image, depth, gt_image, gt_depth, mask, lambda_dssim)

@@ -316,6 +316,8 @@ typedef struct EagsMappingLoss {
     const float* gt_image; /* (3,H,W) */
     const float* gt_depth; /* (1,H,W) */
     const uint8_t* mask;   /* (H,W) 0/1 or NULL (all valid) */
+    int32_t valid_depth_mask; /* 1: the mask of mapper.py:159, (gt_depth > 0) & ~isnan(depth), formed per pixel
+                                 inside the kernels (AND-ed with `mask` when that is given); 0: `mask` only */
 } EagsMappingLoss;
 size_t eags_mapping_loss_scratch_bytes(int32_t width, int32_t height);
 int eags_mapping_loss_forward(const EagsMappingLoss* in, void* scratch, float* out8, void* stream);

@@ -132,3 +132,28 @@ def test_fused_mapping_losses_equal_the_separate_kernels_and_are_reproducible():
         mapping_losses(img0, dep0[:, :8], gt, gt_d, None, 0.2)
     with pytest.raises(RuntimeError, match="CUDA"):
         mapping_losses(img0.cpu(), dep0.cpu(), gt.cpu(), gt_d.cpu(), None, 0.2)
+
+
+def test_fused_mapping_losses_with_the_mappers_own_mask():
+    """mask="valid_depth": (gt_depth > 0) & ~isnan(depth) (mapper.py:159) formed inside the kernels; holes in
+    gt_depth and nan pixels in the rendered depth, against the reference's expression (golden `vd_*`), and equal
+    to passing that mask as a tensor."""
+    from eags_raster.losses import mapping_losses
+    gt, gt_d = torch.from_numpy(ML["vd_gt"]).cuda(), torch.from_numpy(ML["vd_gt_depth"]).cuda()
+    res = []
+    for mask in ("valid_depth", torch.from_numpy(ML["vd_mask"]).cuda()):
+        img = torch.from_numpy(ML["vd_img"]).cuda().requires_grad_(True)
+        dep = torch.from_numpy(ML["vd_depth"]).cuda().requires_grad_(True)
+        c, d = mapping_losses(img, dep, gt, gt_d, mask, 0.2)
+        assert abs(float(c) - float(ML["vd_color_loss"])) < 2e-6
+        assert abs(float(d) - float(ML["vd_depth_loss"])) <= 2e-6 * float(ML["vd_depth_loss"])
+        (2.0 * c + 3.0 * d).backward()
+        ref_i, ref_d = ML["vd_grad_img"], ML["vd_grad_depth"]
+        assert not torch.isnan(img.grad).any() and not torch.isnan(dep.grad).any()
+        assert np.abs(img.grad.cpu().numpy() - ref_i).max() < 1e-4 * np.abs(ref_i).max()
+        assert np.abs(dep.grad.cpu().numpy() - ref_d).max() <= 1e-6 * np.abs(ref_d).max()
+        res.append((c.item(), d.item(), img.grad.clone(), dep.grad.clone()))
+    assert res[0][0] == res[1][0] and res[0][1] == res[1][1]
+    assert torch.equal(res[0][2], res[1][2]) and torch.equal(res[0][3], res[1][3])
+    with pytest.raises(ValueError):
+        mapping_losses(res[0][2], res[0][3], gt, gt_d, "depth", 0.2)
