@@ -364,6 +364,29 @@ int eags_image_l1_forward(const EagsImageL1* in, float* g_color, float* g_depth,
     return 0;
 }
 
+int eags_image_l1_forward_static(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
+                                 float* sums4, void* stream) {
+    if (!in || in->width <= 0 || in->height <= 0 || !in->color || !in->depth || !in->gt_color ||
+        !in->gt_depth || !g_color || !g_depth || !sums4 || (in->soft_alpha && !in->alpha))
+        return fail(EAGS_ERR_INVALID, "eags_image_l1_forward_static: bad argument");
+    if ((long long)in->width * in->height > (long long)EAGS_IMAGE_L1_STATIC_MAX_PIXELS)
+        return fail(EAGS_ERR_INVALID, "eags_image_l1_forward_static: image larger than EAGS_IMAGE_L1_STATIC_MAX_PIXELS "
+                                      "(4194304 pixels); use eags_image_l1_forward with caller-owned scratch");
+    cudaStream_t s = (cudaStream_t)stream;
+    // (no ScopedSpan: the kernel_timing option creates CUDA events, and this entry point creates nothing)
+    const int n = launch_image_l1_fwd_static(in->width, in->height, in->soft_alpha, in->mask_color, in->norm_mode,
+                                             in->eps, in->color, in->depth, in->alpha, in->gt_color, in->gt_depth,
+                                             in->mask, in->mask_depth, in->alpha_min, g_color, g_depth, g_alpha, sums4, s);
+    if (n == -2) {
+        cudaGetLastError();
+        return fail(EAGS_ERR_INVALID, "eags_image_l1_forward_static: cudaGetSymbolAddress of the library's scratch array "
+                                      "failed on the current device");
+    }
+    if (n < 0) return fail_cuda("image_l1_fwd (static scratch)");
+    g_launches.fetch_add((unsigned)n);
+    return 0;
+}
+
 int eags_image_l1_backward(int32_t W, int32_t H, const float* sums4, const float* up_color,
                            const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
                            void* stream) {

@@ -99,6 +99,10 @@ int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_m
                         const float* color, const float* depth, const float* alpha, const float* gt_color,
                         const float* gt_depth, const uint8_t* mask, const uint8_t* mask_depth, float alpha_min,
                         float* g_color, float* g_depth, float* g_alpha, void* scratch, float* out4, cudaStream_t s);
+int launch_image_l1_fwd_static(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
+                               const float* color, const float* depth, const float* alpha, const float* gt_color,
+                               const float* gt_depth, const uint8_t* mask, const uint8_t* mask_depth, float alpha_min,
+                               float* g_color, float* g_depth, float* g_alpha, float* out4, cudaStream_t s);
 int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,
                           float* g_color, float* g_depth, float* g_alpha, cudaStream_t s);
 

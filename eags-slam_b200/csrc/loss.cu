@@ -10,6 +10,7 @@
 //   K10 image_l1_scale : scales the raw gradients by upstream_grad / normaliser (device scalars).
 // HBM-bound streaming: 9 floats + 1 mask byte read, 5 floats written per pixel.
 #include <initializer_list>
+#include <mutex>
 
 #include "kernels.h"
 
@@ -265,6 +266,48 @@ int launch_image_l1_fwd(int W, int H, int soft_alpha, int mask_color, int norm_m
     if (vec) image_l1_fwd_kernel<true><<<grid, LOSS_THREADS, 0, s>>>(a);
     else image_l1_fwd_kernel<false><<<grid, LOSS_THREADS, 0, s>>>(a);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ---- image_l1_fwd with library-owned scratch (eags_image_l1_forward_static) ------------------------------
+// For callers that may not allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc): the
+// kernel's scratch -- the 256-byte ticket line and the per-CTA partial sums -- lives in this file-scope device
+// array instead of a caller buffer.  38 144 bytes, held by every GPU that loads the library until the process
+// exits.  ALL calls share it: two calls that overlap on the GPU (different streams) race on the ticket and the
+// partials; calls on one stream are ordered and each one clears the ticket first (the partials are overwritten
+// before they are read).
+constexpr size_t L1_STATIC_BYTES = 256 + (size_t)148 * 8 * 4 * sizeof(double);   // == image_l1_scratch_bytes()
+static __device__ __align__(256) unsigned char g_l1_static_scratch[L1_STATIC_BYTES];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_l1_static_mutex;
+void* g_l1_static_ptr[MAX_DEVICES];      // device address of the array on each device, resolved once per device
+}  // namespace
+
+// In host code `g_l1_static_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, asked
+// once per device with that device current.  Returns nullptr (and leaves the CUDA error set) on failure.
+static void* l1_static_scratch_for_current_device() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return nullptr;
+    std::lock_guard<std::mutex> lock(g_l1_static_mutex);
+    if (!g_l1_static_ptr[dev]) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_l1_static_scratch) != cudaSuccess || !p) return nullptr;
+        g_l1_static_ptr[dev] = p;
+    }
+    return g_l1_static_ptr[dev];
+}
+
+// -2: the scratch address could not be resolved; otherwise as launch_image_l1_fwd.  No allocation of any kind.
+int launch_image_l1_fwd_static(int W, int H, int soft_alpha, int mask_color, int norm_mode, float eps,
+                               const float* color, const float* depth, const float* alpha, const float* gt_color,
+                               const float* gt_depth, const uint8_t* mask, const uint8_t* mask_depth, float alpha_min,
+                               float* g_color, float* g_depth, float* g_alpha, float* out4, cudaStream_t s) {
+    static_assert(L1_STATIC_BYTES % 256 == 0, "whole 256-byte lines");
+    void* scratch = l1_static_scratch_for_current_device();
+    if (!scratch || image_l1_scratch_bytes(W, H) > L1_STATIC_BYTES) return -2;
+    return launch_image_l1_fwd(W, H, soft_alpha, mask_color, norm_mode, eps, color, depth, alpha, gt_color, gt_depth,
+                               mask, mask_depth, alpha_min, g_color, g_depth, g_alpha, scratch, out4, s);
 }
 
 int launch_image_l1_scale(int W, int H, const float* sums, const float* up_c, const float* up_d,

@@ -112,6 +112,8 @@ SIGNATURES = {
     "eags_image_l1_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "eags_image_l1_forward": (C.c_int, [C.POINTER(EagsImageL1), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_void_p]),
+    "eags_image_l1_forward_static": (C.c_int, [C.POINTER(EagsImageL1), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p]),
     "eags_image_l1_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "eags_ssim_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),

@@ -288,6 +288,23 @@ int eags_image_l1_backward(int32_t width, int32_t height, const float* sums4, co
                            const float* up_depth, float* g_color, float* g_depth, float* g_alpha,
                            void* stream);
 
+/* eags_image_l1_forward without ANY allocation and without a caller scratch buffer.  This entry point has no
+ * counterpart in the reference; it was added for callers that cannot
+ * call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, outputs and arithmetic as eags_image_l1_forward (bit-identical results), minus `scratch`: the
+ * kernel's ticket line and per-CTA partial sums live in a static device array of the library (38 144 bytes,
+ * held by every GPU that loads the library until the process exits; its address is resolved once per device
+ * with cudaGetSymbolAddress).  Limit: width x height <= EAGS_IMAGE_L1_STATIC_MAX_PIXELS (2048 x 2048; the
+ * reference's largest image is 1752 x 1168) -- larger images are rejected with EAGS_ERR_INVALID and a message.
+ * All calls share the array and it keeps the last call's contents (each call clears the ticket line, which is
+ * all that must start at zero): calls on one stream are safe back to back; calls that can OVERLAP on the GPU
+ * (different streams, several host threads on one device) race -- use eags_image_l1_forward with a scratch
+ * buffer per stream for those.  The call itself performs no cudaMalloc / cudaFree and uses no allocating
+ * library routine. */
+#define EAGS_IMAGE_L1_STATIC_MAX_PIXELS 4194304
+int eags_image_l1_forward_static(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
+                                 float* sums4, void* stream);
+
 /* Fused SSIM (11x11 Gaussian window, sigma 1.5, zero padding, mean over C*H*W) -- the `ssim(img1, img2)`
  * of src/entities/losses.py:65-113 as used by the mapping colour loss (src/entities/mapper.py:162-163).
  * Forward writes the mean SSIM to out_mean (device float) and keeps three per-pixel partial maps in
