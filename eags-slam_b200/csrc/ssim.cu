@@ -69,6 +69,32 @@ constexpr int HB = 8;                 // outputs per thread, horizontal pass
 constexpr int VB = 4;                 // outputs per thread, vertical pass
 constexpr int SH_STRIDE = TS + 1;     // row stride of the horizontally filtered tile
 
+// The (32+10)^2 halo tile of NMAPS planes, global -> shared with cp.async (LDGSTS): no register staging, all of a
+// thread's ~7 x NMAPS loads in flight at once (ncu: the staged loop left both kernels waiting on long_scoreboard),
+// zero fill outside the image through the src-size operand (F.conv2d's zero padding).  (r, c) advance
+// incrementally: 256 elements further = 6 rows and 4 columns.
+template <int NMAPS>
+__device__ __forceinline__ void halo_load_async(float (*s_in)[HS][HS + 1], const float* const (&plane)[NMAPS], int H, int W,
+                                                int x0, int y0) {
+    static_assert(SS_THREADS == 6 * HS + 4, "incremental (r, c) step");
+    int r = threadIdx.x / HS, c = threadIdx.x - r * HS;
+    for (int o = threadIdx.x; o < HS * HS; o += SS_THREADS) {
+        const int y = y0 + r - R, x = x0 + c - R;
+        const bool in = y >= 0 && y < H && x >= 0 && x < W;
+        const size_t off = in ? (size_t)y * W + x : 0;
+        const unsigned nbytes = in ? 4u : 0u;
+#pragma unroll
+        for (int m = 0; m < NMAPS; m++) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(&s_in[m][r][c]);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(plane[m] + off), "r"(nbytes) : "memory");
+        }
+        r += 6; c += 4;
+        if (c >= HS) { c -= HS; r += 1; }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 // s_h[q][r][c0 + j] = sum_k g[k] * f_q(in[r][c0 + j + k]) for the NQ quantities produced by `emit`
 template <int NIN, int NQ, typename Emit>
 __device__ __forceinline__ void horizontal_pass(const float (*s_in)[HS][HS + 1], float (*s_h)[HS][SH_STRIDE],
@@ -130,12 +156,9 @@ ssim_fwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const float* p1 = img1 + (size_t)ch * H * W;
     const float* p2 = img2 + (size_t)ch * H * W;
-    for (int o = threadIdx.x; o < HS * HS; o += SS_THREADS) {
-        const int r = o / HS, c = o - r * HS;
-        const int y = y0 + r - R, x = x0 + c - R;
-        float a = 0.f, b = 0.f;   // zero padding (F.conv2d padding = window_size // 2)
-        if (y >= 0 && y < H && x >= 0 && x < W) { a = p1[(size_t)y * W + x]; b = p2[(size_t)y * W + x]; }
-        s_in[0][r][c] = a; s_in[1][r][c] = b;
+    {
+        const float* const planes[2] = {p1, p2};
+        halo_load_async<2>(s_in, planes, H, W, x0, y0);
     }
     __syncthreads();
     horizontal_pass<2, 5>(s_in, s_h, w, [](const float in[2], float f[5]) {
@@ -269,15 +292,9 @@ ssim_bwd_kernel(int C, int H, int W, const float* __restrict__ img1, const float
     __shared__ float s_h[3][HS][SH_STRIDE];
     const int ch = blockIdx.z, x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const size_t plane = (size_t)ch * H * W;
-    for (int o = threadIdx.x; o < HS * HS; o += SS_THREADS) {
-        const int r = o / HS, c = o - r * HS;
-        const int y = y0 + r - R, x = x0 + c - R;
-        float a = 0.f, b = 0.f, cc = 0.f;
-        if (y >= 0 && y < H && x >= 0 && x < W) {
-            const size_t pix = plane + (size_t)y * W + x;
-            a = part_a[pix]; b = part_b[pix]; cc = part_c[pix];
-        }
-        s_in[0][r][c] = a; s_in[1][r][c] = b; s_in[2][r][c] = cc;
+    {
+        const float* const planes[3] = {part_a + plane, part_b + plane, part_c + plane};
+        halo_load_async<3>(s_in, planes, H, W, x0, y0);
     }
     __syncthreads();
     horizontal_pass<3, 3>(s_in, s_h, w, [](const float in[3], float f[3]) { f[0] = in[0]; f[1] = in[1]; f[2] = in[2]; });
