@@ -899,6 +899,10 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
     # (every rank runs them -- the step is collective; rank 0 reports its own)
     from eags_raster import _lib as _l
     spans_ms, n_sp = {}, 3
+    barrier()                 # (rank 0 just joined its clock sampler: without this the others wait for it in-kernel)
+    job.step()
+    torch.cuda.synchronize()
+    barrier()
     _l.set_option("kernel_timing", 1)
     try:
         for _ in range(n_sp):
@@ -908,6 +912,20 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
                 spans_ms[name] = spans_ms.get(name, 0.0) + t_ / n_sp
     finally:
         _l.set_option("kernel_timing", 0)
+    # per rank: the device time of its own views' kernels (everything but the collective kernel) and of the
+    # collective kernel, which opens with a wait for ALL ranks' scatters: a rank whose view is cheap shows the
+    # difference to the slowest rank as time inside peer_adam / peer_reduce
+    own_ms = sum(v for k, v in spans_ms.items() if not k.startswith("peer_"))
+    coll_ms = sum(v for k, v in spans_ms.items() if k.startswith("peer_"))
+    per_rank = None
+    if world > 1:
+        pr = torch.zeros(world, 2, device=dev, dtype=torch.float64)
+        pr[rank, 0], pr[rank, 1] = own_ms, coll_ms
+        dist.all_reduce(pr)
+        per_rank = {"own_kernels_ms": [round(float(v), 4) for v in pr[:, 0]],
+                    "collective_kernel_ms": [round(float(v), 4) for v in pr[:, 1]],
+                    "note": "eager steps with per-launcher events (host launch skew between ranks included); the collective "
+                            "kernel's time on a rank includes its wait for the slowest rank's scatter"}
     barrier()
     err_after = job.ex.error_flag() if fused else 0
     finite = bool(all(torch.isfinite(v).all() for v in job.params().values()))
@@ -968,6 +986,7 @@ def mapping_line(args, world, rank, local, dev, peaks, steps, warmup, in_job_n1=
                          "with `mapping.value` of the --gpus 1 line; the --gpus 1 line's own `value` is the c2 rasterizer "
                          "fwd+bwd metric (BASELINE.json's headline), a different workload and unit"),
         "kernels_ms_per_step_rank0": {k: round(v, 4) for k, v in spans_ms.items()},
+        "kernels_ms_per_step_by_rank": per_rank,
     }
 
 

@@ -37,7 +37,7 @@ constexpr int SCAN_THREADS = 1024;
 // 1 024 -- no inter-CTA dependency, no second kernel.  Because later CTAs still read the counts, the scatter
 // cursor of the exact path goes to word 1 of the tile's line instead of overwriting the count in word 0.
 __global__ void __launch_bounds__(SCAN_THREADS)
-tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
+tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky, unsigned long long* status_host, int status_words) {
     __shared__ unsigned s_warp[SCAN_THREADS / 32];
     __shared__ unsigned s_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -90,17 +90,28 @@ tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky) {
         }
     }
     if (t == img.G - 1) img.ctrl->num_scanned = start + c;
-    if (sticky) {
-        // persistent high-water marks over every forward that was handed this block (CUDA-graph replays: the
-        // owner of the graph looks at it once per frame, an overflow in ANY replay must still show); folded in
-        // by the last CTA to finish, when max_tile is final
+    if (sticky || status_host) {
+        // the last CTA to finish (max_tile, n_big, num_scanned are final then):
+        //  * sticky: persistent high-water marks over every forward that was handed this block (CUDA-graph
+        //    replays: the owner of the graph looks at it once per frame, an overflow in ANY replay must still show);
+        //  * status_host: the caller's status block in mapped pinned HOST memory is written from here.  It used to
+        //    be a cudaMemcpyAsync node between this kernel and the sort: 13 us of copy-engine round trip on the
+        //    critical path of every forward (torch.profiler gap list, profiles/r2/mapping_glue_graph.txt).
         __threadfence();
         __syncthreads();
         if (tid == 0 && atomicAdd(&img.ctrl->work_sort, 1u) == gridDim.x - 1) {
             __threadfence();
-            atomicMax(&sticky->num_rendered, img.ctrl->num_rendered);
-            atomicMax(&sticky->max_tile, *(volatile unsigned*)&img.ctrl->max_tile);
-            atomicOr(&sticky->bucket_overflow, img.ctrl->bucket_overflow);
+            if (sticky) {
+                atomicMax(&sticky->num_rendered, img.ctrl->num_rendered);
+                atomicMax(&sticky->max_tile, *(volatile unsigned*)&img.ctrl->max_tile);
+                atomicOr(&sticky->bucket_overflow, img.ctrl->bucket_overflow);
+            }
+            if (status_host) {
+                const volatile unsigned long long* src =
+                    reinterpret_cast<const volatile unsigned long long*>(sticky ? (void*)sticky : (void*)img.ctrl);
+                for (int k = 0; k < status_words; k++) status_host[k] = src[k];
+                __threadfence_system();
+            }
         }
     }
 }
@@ -651,8 +662,9 @@ pack_flat_kernel(ImagePtrs img, long long capacity, unsigned tile_cap, PackArgs 
 
 }  // namespace
 
-int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s) {
-    tile_scan_kernel<<<(img.G + SCAN_THREADS - 1) / SCAN_THREADS, SCAN_THREADS, 0, s>>>(img, sticky);
+int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, void* status_host, size_t status_bytes, cudaStream_t s) {
+    tile_scan_kernel<<<(img.G + SCAN_THREADS - 1) / SCAN_THREADS, SCAN_THREADS, 0, s>>>(
+        img, sticky, (unsigned long long*)status_host, (int)(status_bytes / 8));
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

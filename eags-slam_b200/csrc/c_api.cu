@@ -165,8 +165,19 @@ static int forward_geom_impl(const EagsView* view, const EagsGaussians* g, void*
     // ctrl + tile_count are contiguous: one memset node
     CHECK_CUDA(cudaMemsetAsync(image_state, 0, IL.tile_count + (size_t)IL.G * 4 * EAGS_CTR_STRIDE, s), "memset(ctrl)");
     CHECK_LAUNCH(launch_preprocess_fwd(*view, *g, geom, img, radii, bucket, (unsigned)tile_cap, g_opt_agg.load(), s), "preprocess_fwd");
-    CHECK_LAUNCH(launch_tile_scan(img, (EagsCtrl*)sticky_dev, s), "tile_scan");
-    if (ctrl_pinned)
+    // The status block goes to the host from inside tile_scan when the caller's buffer is pinned host memory the
+    // device can address (every cudaHostAlloc / cudaHostRegister'ed block under unified addressing; torch's
+    // pin_memory()); anything else (pageable memory) keeps the copy node.
+    void* status_dev = nullptr;
+    if (ctrl_pinned && ctrl_bytes % 8 == 0 && ctrl_bytes <= sizeof(EagsCtrl)) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, ctrl_pinned) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+            status_dev = at.devicePointer;
+        else
+            cudaGetLastError();
+    }
+    CHECK_LAUNCH(launch_tile_scan(img, (EagsCtrl*)sticky_dev, status_dev, ctrl_bytes, s), "tile_scan");
+    if (ctrl_pinned && !status_dev)
         CHECK_CUDA(cudaMemcpyAsync(ctrl_pinned, sticky_dev ? sticky_dev : (void*)img.ctrl, ctrl_bytes,
                                    cudaMemcpyDeviceToHost, s), "memcpy(ctrl)");
     return 0;

@@ -80,7 +80,7 @@ static inline BinningPtrs binning_ptrs(void* base, int64_t cap, int with_keys, i
 int launch_preprocess_fwd(const EagsView& v, const EagsGaussians& g, GeomPtrs geom, ImagePtrs img,
                           int32_t* radii, unsigned long long* bucket, unsigned tile_cap, int aggregate,
                           cudaStream_t s);
-int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, cudaStream_t s);
+int launch_tile_scan(ImagePtrs img, EagsCtrl* sticky, void* status_host, size_t status_bytes, cudaStream_t s);
 int launch_duplicate(const EagsView& v, int P, const int32_t* radii, GeomPtrs geom, ImagePtrs img,
                      BinningPtrs bin, cudaStream_t s);
 int launch_sort_pack(GeomPtrs geom, int P, ImagePtrs img, BinningPtrs bin, unsigned tile_cap, int use_radix,

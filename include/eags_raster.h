@@ -144,7 +144,8 @@ int eags_forward_render(const EagsView* view, const EagsGaussians* g, const int3
  * path; the tile scan of stage 1 is still valid).  tile_cap == 0 degenerates to the exact path.
  * `sticky_status_dev` (optional, device, 64 bytes, zeroed ONCE by the caller and never by the library): when
  * given, num_rendered / max_tile are folded into it with atomicMax and bucket_overflow with atomicOr, and
- * THAT block is what is copied to `status_pinned` -- for CUDA-graph replays, where the host looks at the
+ * THAT block is what reaches `status_pinned` (stored by the tile scan's last CTA when the block is pinned host
+ * memory the device can address, copied by a cudaMemcpyAsync otherwise) -- for CUDA-graph replays, where the host looks at the
  * status once per many replays and an overflow of any of them must still be seen. */
 typedef struct EagsForwardStatus {
     uint64_t num_rendered;    /* K = sum(tiles_touched)                                   */
