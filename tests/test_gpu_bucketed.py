@@ -50,3 +50,21 @@ def test_bucketed_equals_exact(name, P):
         assert rz._tile_cap[key] > 64
     finally:
         rz.set_bucketed(True)
+
+
+def test_status_block_reaches_pinned_and_pageable_host_memory(monkeypatch):
+    """The forward's status block (K, largest tile, overflow flag) is stored to the caller's buffer by the tile
+    scan itself when that buffer is pinned host memory, and copied by a cudaMemcpyAsync node when it is pageable:
+    both must report the same K and render the same image."""
+    sc = scene.make_scene("ragged", P=3000, seed=4)
+    cam = scene.workload_camera("ragged")
+    rz.set_bucketed(True)
+    ref_out, _ = _run(cam, sc)
+    ref_out, _ = _run(cam, sc)                           # second call: bucketed, pinned status (the default)
+    pageable = torch.zeros(8, dtype=torch.int64)
+    assert not pageable.is_pinned()
+    monkeypatch.setattr(rz, "_pinned_status", lambda: pageable)
+    pageable.fill_(-1)
+    out, _ = _run(cam, sc)
+    assert out[5].num_rendered == ref_out[5].num_rendered > 0 and int(pageable[0]) == out[5].num_rendered
+    assert torch.equal(out[0], ref_out[0]) and torch.equal(out[1], ref_out[1])
