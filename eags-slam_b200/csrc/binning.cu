@@ -109,8 +109,9 @@ tile_scan_kernel(ImagePtrs img, EagsCtrl* sticky, unsigned long long* status_hos
             if (status_host) {
                 const volatile unsigned long long* src =
                     reinterpret_cast<const volatile unsigned long long*>(sticky ? (void*)sticky : (void*)img.ctrl);
+                // (no system-scope fence: the host reads the block only after an event / stream synchronisation
+                // behind this kernel, which orders the stores; a fence here would hold the kernel for a PCIe round trip)
                 for (int k = 0; k < status_words; k++) status_host[k] = src[k];
-                __threadfence_system();
             }
         }
     }
