@@ -8,16 +8,20 @@
 //   K2 tile_scan   : exclusive scan of the per-tile key counts (counted by preprocess_fwd) ->
 //                    `ranges` (== identifyTileRanges output, (0,0) for empty tiles) + scatter cursors;
 //                    one CTA per 1 024 tiles, each re-summing the counts before its own.
+//                    The last CTA to finish also stores the forward's status block (K, largest tile,
+//                    overflow flag) into the caller's mapped pinned host block.
 //   K3 duplicate   : (preprocess.cu) scatters (depth_bits << 32 | gaussian) into the tile's bucket.
-//   K4 sort_pack   : one CTA per tile sorts its bucket in shared memory -- an LSD radix sort over the
-//                    depth bits that actually vary inside the tile (8-bit digits, warp-level
-//                    match_any ranking, Gaussian index as payload: 3 passes for a tile spanning
-//                    1..4 m), then orders exact depth ties by Gaussian index, which inside one tile
-//                    IS upstream's emission order, so the result equals upstream's stable radix sort
-//                    of (tile | depth) keys bit for bit -- then gathers each splat's attributes once
-//                    and writes the packed, sorted splat stream (48 B records) that blend_fwd /
-//                    blend_bwd stream with TMA bulk copies.  Tie runs longer than 32 keys (degenerate
-//                    inputs) fall back to a bitonic network on the 64-bit (depth | index) composite.
+//   K4 sort_pack   : one CTA per tile sorts its bucket in shared memory.  Default (sort mode 2): a
+//                    one-pass bucket sort over the tile's own depth range with a thread-local insertion
+//                    finish; clustered depths fall back to an LSD radix sort over the depth bits that
+//                    actually vary inside the tile (8-bit digits, warp-level match_any ranking, Gaussian
+//                    index as payload), tie runs longer than 32 keys to a bitonic network on the 64-bit
+//                    (depth | index) composite.  Exact depth ties are ordered by Gaussian index, which
+//                    inside one tile IS upstream's emission order, so the result equals upstream's
+//                    stable radix sort of (tile | depth) keys bit for bit.  The CTAs write the sorted
+//                    index list (+ optional keys); pack_flat_kernel then gathers each splat's 48-byte
+//                    record over the whole list at once -> the packed, sorted splat stream that
+//                    blend_fwd / blend_bwd stream with TMA bulk copies.
 //                    Tiles with more than EAGS_SORT_SMALL_CAP keys go to a persistent 1024-thread
 //                    variant with 128 KB of shared memory; beyond EAGS_SORT_BIG_CAP the bitonic
 //                    network runs in global memory (correct, slow, never seen in SLAM submaps).
@@ -26,7 +30,7 @@
 namespace {
 
 // ------------------------------------------------------------------------------------------------
-// K2: single-CTA scan over G tile counts (G = 1 200 .. 8 030 for the benchmark shapes).
+// K2: scan over G tile counts (G = 1 200 .. 8 030 for the benchmark shapes).
 // ------------------------------------------------------------------------------------------------
 constexpr int SCAN_THREADS = 1024;
 

@@ -11,6 +11,10 @@
 // multi-buffered so the copy of batch b+2 overlaps the blending of batch b.  Upstream instead gathers
 // id -> xy / conic / colour / depth from four arrays behind a __syncthreads per batch.
 //
+// Each warp owns an 8x4 pixel block.  Per batch it culls one splat per lane against the block (exact-arithmetic-
+// independent, conservative), and blend_fwd then walks a compacted list of the survivors' shared-memory record
+// addresses (one broadcast LDS per survivor instead of a bitmask walk); blend_bwd walks the ballot masks.
+//
 // blend_bwd replaces upstream's 10 global atomics per (pixel, Gaussian) pair by
 //   (1) a pixel-per-lane pass that forms only two scalars per pair (gG = dL/dG * G and w = alpha * T;
 //       dL/dalpha in suffix-sum form needs one running scalar instead of five accumulators),
