@@ -49,6 +49,12 @@ for r in rows[2:]:
         continue
     traffic[key] = num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum")
     pct[key] = {k: num(r, m) for k, m in PCT.items() if m in hdr}
+# the record gather of sort_pack is its own kernel (pack_flat_kernel): its DRAM bytes belong to the sort_pack row
+for r in rows[2:]:
+    if "pack_flat" in r[hdr.index("Kernel Name")] and "sort_pack" in traffic:
+        traffic["sort_pack"] += num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum")
+        pct["sort_pack"]["pack_flat_duration_us_under_ncu"] = num(r, "gpu__time_duration.sum")
+        break
 path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
 d = json.load(open(path)) if os.path.exists(path) else {}
 d[wl] = traffic
