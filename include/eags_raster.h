@@ -301,7 +301,8 @@ int eags_image_l1_backward(int32_t width, int32_t height, const float* sums4, co
  * all that must start at zero): calls on one stream are safe back to back; calls that can OVERLAP on the GPU
  * (different streams, several host threads on one device) race -- use eags_image_l1_forward with a scratch
  * buffer per stream for those.  The call itself performs no cudaMalloc / cudaFree and uses no allocating
- * library routine. */
+ * library routine.  The FIRST call on a device resolves the array's address (and, under CUDA's lazy module
+ * loading, loads the kernel): make that one call before a stream capture begins, not inside it. */
 #define EAGS_IMAGE_L1_STATIC_MAX_PIXELS 4194304
 int eags_image_l1_forward_static(const EagsImageL1* in, float* g_color, float* g_depth, float* g_alpha,
                                  float* sums4, void* stream);
