@@ -20,7 +20,7 @@ single-GPU parity test of the exchange (ranks run one after the other).
 from __future__ import annotations
 
 import ctypes as C
-from typing import List, Optional
+from typing import Optional
 
 import torch
 
